@@ -1,0 +1,150 @@
+"""Optimizers and the distributed wrapper.
+
+``DistributedOptimizer(opt, op=Average|Adasum)`` is the reference's only
+parallelism strategy: replicate the model, reduce every gradient across ranks
+before the update (``horovod/tensorflow_mnist.py:132-136``;
+``horovod/tensorflow_mnist_gpu.py:136-138``).
+
+Two forms:
+
+* wrapping a ``torch.optim.Optimizer`` — generic: gradients are packed into
+  flat buckets (reverse parameter order, like backward produces them), reduced
+  with :func:`b200dp.allreduce_`, unpacked, then the inner optimizer steps;
+* wrapping :class:`Adam` (a plain config) — the engines fuse the reduction, the
+  1/size scale and the Adam update into one peer-memory kernel per bucket.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, replace
+from typing import Iterable, List, Optional, Tuple
+
+import torch
+
+from ..runtime import world as _w
+from . import collectives as C
+from .buckets import plan_buckets
+
+
+@dataclass(frozen=True)
+class Adam:
+    """Adam hyper-parameters.  Defaults follow ``tf.train.AdamOptimizer``
+    (epsilon 1e-8, TF epsilon placement); ``Adam.keras()`` gives Keras' 1e-7."""
+    lr: float = 0.001
+    beta1: float = 0.9
+    beta2: float = 0.999
+    epsilon: float = 1e-8
+    eps_mode: str = "tf"
+
+    @staticmethod
+    def keras(lr: float = 0.001) -> "Adam":
+        return Adam(lr=lr, epsilon=1e-7)
+
+    def scaled(self, factor: float) -> "Adam":
+        return replace(self, lr=self.lr * factor)
+
+
+def lr_scaler(use_adasum: bool = False) -> int:
+    """The reference's rule (``horovod/tensorflow_mnist.py:123-127``): scale the LR
+    by the world size; with Adasum by ``local_size`` when the GPU collective path
+    is built, else by 1."""
+    if use_adasum:
+        return _w.local_size() if _w.nccl_built() else 1
+    return _w.size()
+
+
+@dataclass(frozen=True)
+class DistributedAdam:
+    """What ``DistributedOptimizer(Adam(...))`` returns: config consumed by engines."""
+    base: Adam
+    op: C.ReduceOp = C.Average
+    wire_dtype: str = "fp32"          # "fp32" | "bf16" gradients on the wire
+    algo: str = "auto"                # auto | oneshot | twoshot | nvls
+
+    @property
+    def lr(self) -> float:
+        return self.base.lr
+
+
+def fusion_threshold_bytes() -> int:
+    v = os.environ.get("B200DP_FUSION_THRESHOLD", os.environ.get("HOROVOD_FUSION_THRESHOLD"))
+    return int(v) if v else 64 * 1024 * 1024
+
+
+class _DistributedTorchOptimizer:
+    """Generic wrapper around any ``torch.optim.Optimizer``."""
+
+    def __init__(self, optimizer: torch.optim.Optimizer, named_parameters=None, op: C.ReduceOp = C.Average,
+                 bucket_bytes: Optional[int] = None):
+        self._opt = optimizer
+        self.op = op
+        params: List[torch.nn.Parameter] = []
+        for g in optimizer.param_groups:
+            params.extend(p for p in g["params"] if p.requires_grad)
+        self._params = params
+        sizes = [p.numel() * 4 for p in reversed(params)]
+        self._bucket_ix = plan_buckets(sizes, bucket_bytes or fusion_threshold_bytes())
+        self._rev = list(reversed(params))
+        self._synced = False
+
+    # torch optimizer surface -------------------------------------------------
+    @property
+    def param_groups(self):
+        return self._opt.param_groups
+
+    @property
+    def state(self):
+        return self._opt.state
+
+    def state_dict(self):
+        return self._opt.state_dict()
+
+    def load_state_dict(self, sd):
+        return self._opt.load_state_dict(sd)
+
+    def zero_grad(self, set_to_none: bool = True):
+        self._synced = False
+        return self._opt.zero_grad(set_to_none=set_to_none)
+
+    def __getattr__(self, item):
+        return getattr(self._opt, item)
+
+    # -------------------------------------------------------------------------
+    def synchronize(self) -> None:
+        """Reduce all gradients now (bucketed, reverse order)."""
+        if _w.size() == 1:
+            self._synced = True
+            return
+        for ix in self._bucket_ix:
+            ps = [self._rev[i] for i in ix]
+            ps = [p for p in ps if p.grad is not None]
+            if not ps:
+                continue
+            dev = ps[0].grad.device
+            flat = torch.cat([p.grad.detach().reshape(-1).float() for p in ps]).to(dev)
+            C.allreduce_(flat, self.op, segments=[p.numel() for p in ps])
+            off = 0
+            for p in ps:
+                n = p.numel()
+                p.grad.copy_(flat[off:off + n].view_as(p.grad))
+                off += n
+        self._synced = True
+
+    def step(self, closure=None):
+        if not self._synced:
+            self.synchronize()
+        self._synced = False
+        return self._opt.step(closure) if closure is not None else self._opt.step()
+
+
+def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Average, *,
+                         wire_dtype: str = "fp32", algo: str = "auto", bucket_bytes: Optional[int] = None):
+    """Horovod-named factory (see module docstring)."""
+    if isinstance(optimizer, DistributedAdam):
+        return optimizer
+    if isinstance(optimizer, Adam):
+        algo = os.environ.get("B200DP_ALLREDUCE_ALGO", algo)
+        return DistributedAdam(base=optimizer, op=op, wire_dtype=wire_dtype, algo=algo)
+    if isinstance(optimizer, torch.optim.Optimizer):
+        return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes)
+    raise TypeError(f"cannot wrap optimizer of type {type(optimizer).__name__}")

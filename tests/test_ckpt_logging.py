@@ -1,0 +1,109 @@
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200dp as hvd
+from b200dp.ckpt.manager import CheckpointManager, export_model, load_tensors
+from b200dp.utils.eventlog import EventWriter, crc32c, read_events
+from b200dp.utils.logging import JsonLogger
+from b200dp.data import mnist
+
+
+def _state(step, val=1.0):
+    return {"tensors": {"params": torch.full((8,), val), "adam_m": torch.zeros(8), "adam_v": torch.ones(8)},
+            "meta": {"arch": "mnist_cnn", "global_step": step}}
+
+
+def test_roundtrip_bitwise_and_latest_pointer(tmp_path):
+    m = CheckpointManager(str(tmp_path), keep=2, save_secs=None)
+    assert m.latest() is None and m.restore() is None
+    t = torch.randn(1000)
+    p = m.save({"tensors": {"params": t}, "meta": {"x": 1}}, step=7)
+    assert os.path.basename(p) == "ckpt-7.safetensors"
+    r = m.restore()
+    assert torch.equal(r["tensors"]["params"], t) and r["meta"]["step"] == 7 and r["meta"]["x"] == 1
+    assert open(tmp_path / "latest").read() == "ckpt-7.safetensors"
+    for s in (8, 9, 10):
+        m.save(_state(s), s)
+    assert [s for s, _ in m.list()] == [9, 10]             # keep-last-2
+    assert m.latest().endswith("ckpt-10.safetensors")
+    os.remove(tmp_path / "latest")                         # lost pointer -> directory scan
+    assert m.latest().endswith("ckpt-10.safetensors")
+    assert not [f for f in os.listdir(tmp_path) if ".tmp." in f]
+
+
+def test_disabled_manager_is_noop(tmp_path):
+    m = CheckpointManager(None)
+    assert not m.enabled and m.save(_state(1), 1) is None and m.restore() is None and not m.due(5)
+
+
+def test_due_by_steps_and_secs(tmp_path):
+    m = CheckpointManager(str(tmp_path), save_secs=None, save_steps=5)
+    assert not m.due(3) and m.due(5)
+    m.save(_state(5), 5)
+    assert not m.due(5)
+    m2 = CheckpointManager(str(tmp_path / "b"), save_secs=0.0)
+    assert m2.due(1)
+
+
+def test_export_model(tmp_path):
+    p = export_model(str(tmp_path / "final_model"), {"params": torch.arange(4.0)}, {"arch": "mnist_cnn"})
+    t, meta = load_tensors(p)
+    assert torch.equal(t["params"], torch.arange(4.0)) and meta["arch"] == "mnist_cnn"
+    assert json.load(open(tmp_path / "final_model" / "model.json"))["arch"] == "mnist_cnn"
+
+
+def test_json_logger_schema(capsys):
+    buf = io.StringIO()
+    lg = JsonLogger(rank=3, size=8, local_rank=3, stream=buf, tf_style=True)
+    lg.step(10, 0.25, lr=0.008)
+    lg.step(20, torch.tensor(0.125))
+    lines = [json.loads(l) for l in buf.getvalue().splitlines()]
+    assert len(lines) == 2
+    for k in ("ts", "level", "event", "rank", "local_rank", "size", "host", "step", "loss"):
+        assert k in lines[0]
+    assert lines[0]["rank"] == 3 and lines[0]["size"] == 8 and lines[0]["event"] == "train_step"
+    assert lines[1]["loss"] == 0.125
+    err = capsys.readouterr().err
+    assert "INFO:tensorflow:loss = 0.25, step = 10" in err and "sec)" in err.splitlines()[1]
+
+
+def test_logger_level_filter():
+    buf = io.StringIO()
+    lg = JsonLogger(stream=buf, level="WARNING", tf_style=False)
+    lg.info("x"); lg.warning("y")
+    assert [json.loads(l)["event"] for l in buf.getvalue().splitlines()] == ["y"]
+
+
+def test_event_file_roundtrip(tmp_path):
+    assert crc32c(b"123456789") == 0xE3069283
+    w = EventWriter(str(tmp_path))
+    w.add_scalars({"epoch_loss": 0.5, "epoch_accuracy": 0.75}, step=1)
+    w.add_scalars({"epoch_loss": 0.25}, step=2)
+    w.close()
+    ev = read_events(w.path)
+    assert ev[0] == (0, {})
+    assert ev[1][0] == 1 and ev[1][1]["epoch_loss"] == 0.5 and ev[1][1]["epoch_accuracy"] == 0.75
+    assert ev[2] == (2, {"epoch_loss": 0.25})
+    assert len(open(tmp_path / "scalars.jsonl").read().splitlines()) == 2
+
+
+def test_data_pipeline(tmp_path):
+    d = mnist.ensure_cache_dir(str(tmp_path / "a" / "datasets"))
+    assert mnist.ensure_cache_dir(d) == d                              # EEXIST tolerated
+    (xtr, ytr), (xte, yte) = mnist.load_data("MNIST-data-0", cache_dir=d, n_train=300, n_test=50)
+    assert xtr.shape == (300, 28, 28) and xtr.dtype == np.uint8 and yte.shape == (50,)
+    assert os.path.exists(os.path.join(d, "MNIST-data-0.npz"))           # per-rank cache file
+    (xtr2, _), _ = mnist.load_data("MNIST-data-0", cache_dir=d)
+    assert np.array_equal(xtr, xtr2)
+    x = mnist.preprocess(xtr)
+    assert x.shape == (300, 784) and x.dtype == np.float32 and 0 <= x.min() and x.max() <= 1
+    gen = mnist.train_input_generator(x, ytr, batch_size=64, seed=0)
+    seen = [next(gen) for _ in range(9)]
+    assert all(b[0].shape == (64, 784) and b[1].shape == (64,) for b in seen)
+    first_epoch = np.concatenate([b[1] for b in seen[:4]])               # 300//64 = 4 full batches, tail dropped
+    assert len(first_epoch) == 256

@@ -1,0 +1,94 @@
+"""world_size 2 / 4 over the launcher with the gloo backend (SURVEY §4.3 'Distributed (CPU)';
+BASELINE.json config 1: world_size=2 on CPU/gloo, plumbing, no GPU)."""
+import glob
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RUN = [sys.executable, os.path.join(ROOT, "bin", "b200run")]
+W = os.path.join(ROOT, "tests", "workers")
+
+
+def _launch(np_, script_args, timeout=300, extra=(), env=None):
+    e = dict(os.environ, B200DP_LOG_TF_STYLE="0", OMP_NUM_THREADS="2", **(env or {}))
+    return subprocess.run(RUN + ["-np", str(np_), "--cpu", *extra, sys.executable, *script_args],
+                          capture_output=True, text=True, timeout=timeout, env=e, cwd=ROOT)
+
+
+@pytest.mark.parametrize("np_", [2, 4])
+def test_collectives(tmp_path, np_):
+    r = _launch(np_, [os.path.join(W, "collectives_worker.py"), str(tmp_path)])
+    assert r.returncode == 0, r.stderr[-3000:]
+    res = [json.load(open(p)) for p in sorted(glob.glob(str(tmp_path / "r*.json")))]
+    assert len(res) == np_
+    for i, d in enumerate(res):
+        assert d["rank"] == i and d["size"] == np_ and d["local_size"] == np_
+        for k in ("avg_ok", "sum_ok", "input_untouched", "adasum_ok", "bcast_ok", "replicas_identical"):
+            assert d[k], (i, k)
+        assert d["obj"] == 0 and d["gather"] == list(range(np_))
+        assert d["bf16_avg"] == pytest.approx((np_ - 1) / 2)
+
+
+def _example(name, tmp_path, np_, args, env=None, extra=()):
+    return _launch(np_, [os.path.join(ROOT, "examples", name), "--synthetic", "--engine", "torch", "--width", "0.25",
+                         "--train-samples", "512", *args], env=env, extra=extra)
+
+
+def test_session_example_rank0_only_files_and_resume(tmp_path):
+    ck = str(tmp_path / "ck")
+    r = _example("tensorflow_mnist.py", tmp_path, 2, ["--num-steps", "24", "--batch-size", "32", "--checkpoint-dir", ck])
+    assert r.returncode == 0, r.stderr[-3000:]
+    recs = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    steps = {(d["rank"], d["step"]) for d in recs if d["event"] == "train_step"}
+    assert {(0, 1), (1, 1), (0, 11), (1, 11)} <= steps                  # every rank logs every 10 iterations
+    assert max(s for _, s in steps) <= 12                               # 24 // 2 steps
+    saved = [d for d in recs if d["event"] == "checkpoint_saved"]
+    assert saved and all(d["rank"] == 0 for d in saved) and saved[-1]["step"] == 12
+    assert sorted(os.listdir(ck)) == ["ckpt-12.safetensors", "latest"]
+    # restart with a bigger budget: rank 0 restores, broadcast syncs rank 1, both continue from 12
+    r2 = _example("tensorflow_mnist.py", tmp_path, 2, ["--num-steps", "40", "--batch-size", "32", "--checkpoint-dir", ck])
+    assert r2.returncode == 0, r2.stderr[-3000:]
+    recs2 = [json.loads(l) for l in r2.stdout.splitlines() if l.startswith("{")]
+    assert [d for d in recs2 if d["event"] == "checkpoint_restored"][0]["step"] == 12
+    first = {d["rank"]: d["step"] for d in reversed(recs2) if d["event"] == "train_step"}
+    assert first == {0: 13, 1: 13}
+    assert "ckpt-20.safetensors" in os.listdir(ck)
+
+
+def test_keras_example_metric_average_and_export(tmp_path):
+    args = ["--num-steps", "16", "--batch-size", "32", "--test-samples", "64", "--log-dir", str(tmp_path / "logs"),
+            "--checkpoint-dir", str(tmp_path / "ck"), "--export-dir", str(tmp_path / "final_model")]
+    r = _example("tensorflow_mnist_gpu.py", tmp_path, 2, args)
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "Test loss:" in r.stdout and "Test accuracy:" in r.stdout
+    recs = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    ep = [d for d in recs if d["event"] == "epoch_end"]
+    assert ep and all(d["rank"] == 0 for d in ep)                       # verbose only on rank 0
+    assert ep[0]["epochs"] == 2                                          # 16 // (512 // (32*2))
+    assert os.path.exists(tmp_path / "final_model" / "model.safetensors")
+    assert any(f.startswith("events.out.tfevents") for f in os.listdir(tmp_path / "logs"))
+    assert any(f.startswith("mnist-") for f in os.listdir(tmp_path / "ck"))
+
+
+def test_adasum_example_runs(tmp_path):
+    r = _example("tensorflow_mnist.py", tmp_path, 2, ["--num-steps", "8", "--batch-size", "16", "--use-adasum",
+                                                      "--checkpoint-dir", str(tmp_path / "ck")])
+    assert r.returncode == 0, r.stderr[-3000:]
+
+
+def test_killed_rank_fails_job_then_restart_resumes(tmp_path):
+    ck = str(tmp_path / "ck")
+    base = ["--num-steps", "40", "--batch-size", "16", "--checkpoint-dir", ck, "--checkpoint-secs", "0"]
+    r = _example("tensorflow_mnist.py", tmp_path, 2, base, env={"B200DP_FAULT": "1:7"}, extra=["--grace-secs", "2"])
+    assert r.returncode == 17                                            # the dead rank's code propagates
+    assert "terminating" in r.stderr
+    assert any(f.startswith("ckpt-") for f in os.listdir(ck))            # rank 0 had been saving
+    r2 = _example("tensorflow_mnist.py", tmp_path, 2, base, env={"B200DP_FAULT": "1:7"},
+                  extra=["--max-restarts", "1", "--grace-secs", "2"])
+    # first attempt restores (>= step 6), dies again only if it passes step 7 at restart 0; either way ends clean
+    assert r2.returncode == 0, r2.stderr[-3000:]
+    assert "ckpt-20.safetensors" in os.listdir(ck)

@@ -1,0 +1,78 @@
+import os
+import subprocess
+import sys
+import textwrap
+
+import pytest
+
+from b200dp.launch import b200run as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RUN = [sys.executable, os.path.join(ROOT, "bin", "b200run")]
+
+
+def test_parses_the_reference_mpirun_argv():
+    # argv of horovod/tensorflow-mnist.yaml:19-38
+    argv = ["-np", "2", "--allow-run-as-root", "-bind-to", "none", "-map-by", "slot", "-x", "LD_LIBRARY_PATH",
+            "-x", "PATH", "-mca", "pml", "ob1", "-mca", "btl", "^openib", "python", "/examples/tensorflow_mnist.py"]
+    a = L.build_parser().parse_args(argv)
+    assert a.np == 2 and a.allow_run_as_root and a.bind_to == "none" and a.map_by == "slot"
+    assert a.exports == ["LD_LIBRARY_PATH", "PATH"] and a.mca == [["pml", "ob1"], ["btl", "^openib"]]
+    assert a.command == ["python", "/examples/tensorflow_mnist.py"]
+
+
+def test_hostfile_and_slot_mapping():
+    hosts = L.parse_hostfile("# workers\nw0 slots=2\nw1 slots=1\n\nw2:3\n")
+    assert hosts == [("w0", 2), ("w1", 1), ("w2", 3)]
+    slots = L.map_by_slot(hosts, 4)
+    assert [(s.host, s.local_rank, s.local_size) for s in slots] == [("w0", 0, 2), ("w0", 1, 2), ("w1", 0, 1), ("w2", 0, 1)]
+    assert L.parse_hosts_arg("a:2,b") == [("a", 2), ("b", 1)]
+    with pytest.raises(ValueError):
+        L.map_by_slot([("a", 1)], 2)
+
+
+def _run(args, code, timeout=120, env=None):
+    e = dict(os.environ, **(env or {}))
+    return subprocess.run(RUN + args + [sys.executable, "-c", textwrap.dedent(code)], capture_output=True,
+                          text=True, timeout=timeout, env=e)
+
+
+def test_env_export_and_rank_env():
+    r = _run(["-np", "3", "-x", "FOO=bar", "-x", "PATH", "-mca", "pml", "ob1", "--tag-output"], """
+        import os
+        print(os.environ["RANK"], os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"], os.environ["OMPI_COMM_WORLD_RANK"],
+              os.environ["FOO"], os.environ["MASTER_ADDR"])
+    """)
+    assert r.returncode == 0, r.stderr
+    lines = sorted(r.stdout.splitlines())
+    assert lines == [f"[1,{i}]<stdout>:{i} 3 {i} {i} bar 127.0.0.1" for i in range(3)]
+
+
+def test_fail_fast_kills_survivors_and_propagates_code():
+    r = _run(["-np", "3", "--grace-secs", "1"], """
+        import os, sys, time
+        if os.environ["RANK"] == "1":
+            time.sleep(0.3); sys.exit(7)
+        time.sleep(60)
+    """, timeout=30)
+    assert r.returncode == 7
+    assert "rank 1 exited with code 7" in r.stderr
+
+
+def test_max_restarts_reruns_job(tmp_path):
+    marker = tmp_path / "m"
+    r = _run(["-np", "2", "--max-restarts", "2"], f"""
+        import os, sys
+        if os.environ["RANK"] == "0" and os.environ["B200DP_RESTART_COUNT"] == "0":
+            sys.exit(3)
+        if os.environ["RANK"] == "0":
+            open({str(marker)!r}, "w").write(os.environ["B200DP_RESTART_COUNT"])
+    """, timeout=60)
+    assert r.returncode == 0, r.stderr
+    assert marker.read_text() == "1"
+    assert "restart 1/2" in r.stderr
+
+
+def test_no_command_is_an_error():
+    r = subprocess.run(RUN + ["-np", "1"], capture_output=True, text=True)
+    assert r.returncode == 2

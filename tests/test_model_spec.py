@@ -1,0 +1,85 @@
+import math
+
+import pytest
+import torch
+
+from b200dp.models import spec as S
+from b200dp.models import torch_ref
+from b200dp.utils.philox import dropout_keep_mask
+from b200dp.parallel.buckets import plan_buckets, plan_arena_buckets
+
+
+def test_param_counts_match_reference_model():
+    sp = S.get_spec("mnist_cnn")
+    assert sp.num_params == 3_274_634
+    assert sp.fwd_flops_per_image() == 2 * (784 * 25 * 32 + 196 * 800 * 64 + 3136 * 1024 + 1024 * 10)
+    shapes = {p.name: p.shape for p in sp.params}
+    assert shapes["conv1.kernel"] == (5, 5, 1, 32) and shapes["conv2.kernel"] == (5, 5, 32, 64)
+    assert shapes["dense.kernel"] == (3136, 1024) and shapes["out.kernel"] == (1024, 10)
+    assert all(p.offset % S.ALIGN_ELEMS == 0 for p in sp.params)
+    assert S.get_spec("keras128").num_params == 1_199_882
+    assert S.get_spec("mnist_cnn", 6.0).num_params == 117_490_954 or S.get_spec("mnist_cnn", 6.0).num_params > 1e8
+    with pytest.raises(ValueError):
+        S.get_spec("resnet")
+
+
+def test_width_16_param_count():
+    assert abs(S.get_spec("mnist_cnn", 16.0).num_params - 835e6) / 835e6 < 0.01
+
+
+@pytest.mark.parametrize("arch", ["mnist_cnn", "keras128"])
+def test_forward_shapes_and_eval_determinism(arch):
+    sp = S.get_spec(arch, 0.25)
+    flat = S.init_flat(sp, seed=3)
+    x = torch.rand(5, 784)
+    a = torch_ref.forward(sp, sp.views(flat), x, training=False)
+    b = torch_ref.forward(sp, sp.views(flat), x, training=False)
+    assert a.shape == (5, 10) and torch.equal(a, b)
+    t1 = torch_ref.forward(sp, sp.views(flat), x, training=True, seed=1, step=0)
+    t2 = torch_ref.forward(sp, sp.views(flat), x, training=True, seed=1, step=1)
+    assert not torch.equal(t1, t2)                          # dropout mask changes per step
+
+
+def test_philox_mask_statistics_and_determinism():
+    m1 = dropout_keep_mask(100_000, 0.5, seed=7, step=3)
+    m2 = dropout_keep_mask(100_000, 0.5, seed=7, step=3)
+    assert torch.equal(m1, m2)
+    assert abs(m1.float().mean().item() - 0.5) < 0.01
+    assert abs(dropout_keep_mask(100_000, 0.25, 7, 3).float().mean().item() - 0.75) < 0.01
+    assert not torch.equal(m1, dropout_keep_mask(100_000, 0.5, seed=7, step=4))
+    # Philox4x32-10 known-answer test (Random123 kat: counter=0,key=0)
+    from b200dp.utils.philox import philox4x32
+    import numpy as np
+    z = np.zeros(1, np.uint32)
+    out = [int(v[0]) for v in philox4x32(z, z, z, z, 0, 0)]
+    assert out == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+
+
+def test_adam_tf_matches_manual():
+    p = torch.tensor([1.0, -2.0]); g = torch.tensor([0.5, 0.25])
+    m = torch.zeros(2); v = torch.zeros(2)
+    torch_ref.adam_step_(p, g, m, v, 1, lr=0.1)
+    lr_t = 0.1 * math.sqrt(1 - 0.999) / (1 - 0.9)
+    exp = torch.tensor([1.0, -2.0]) - lr_t * (0.1 * g) / ((0.001 * g * g).sqrt() + 1e-8)
+    assert torch.allclose(p, exp, atol=1e-6)
+    # torch placement agrees with torch.optim.Adam
+    w = torch.nn.Parameter(torch.tensor([1.0, -2.0]))
+    o = torch.optim.Adam([w], lr=0.1)
+    w.grad = g.clone(); o.step()
+    p2 = torch.tensor([1.0, -2.0]); m2 = torch.zeros(2); v2 = torch.zeros(2)
+    torch_ref.adam_step_(p2, g, m2, v2, 1, lr=0.1, eps_mode="torch")
+    assert torch.allclose(p2, w.detach(), atol=1e-6)
+
+
+def test_bucket_planner():
+    assert plan_buckets([10, 10, 10], 20) == [[0, 1], [2]]
+    assert plan_buckets([50, 1, 1], 20) == [[0], [1, 2]]
+    assert plan_buckets([], 20) == []
+    sp = S.get_spec()
+    bs = plan_arena_buckets(sp, [["dense.bias", "out."], ["dense.kernel"], ["conv1.", "conv2."]])
+    assert [b.name for b in bs] == ["dense.bias+out.", "dense.kernel", "conv1.+conv2."]
+    assert sum(b.numel for b in bs) == sp.total
+    dk = sp.param("dense.kernel")
+    assert bs[1].start == dk.offset and bs[1].numel >= dk.numel
+    with pytest.raises(ValueError):
+        plan_arena_buckets(sp, [["conv1.", "dense."], ["conv2.", "out."]])
