@@ -1,0 +1,456 @@
+"""The sm_100a training engine for the MNIST CNN family.
+
+One training step (the reference's ``mon_sess.run(train_op)``, ``horovod/tensorflow_mnist.py:168-171``;
+Keras ``fit`` inner loop, ``horovod/tensorflow_mnist_gpu.py:173``) is a fixed sequence of hand-written
+kernels replayed from a CUDA graph:
+
+  fwd : conv1+bias+ReLU+pool (CUDA cores, K=25)  ->  conv2 implicit GEMM + bias+ReLU+pool (tcgen05)
+        ->  dense GEMM, split-K into fp32 (tcgen05)  ->  head: bias+ReLU+dropout+logits+softmax-xent fwd/bwd
+  bwd : head wgrad  ->  dense wgrad (tcgen05, written straight into the gradient arena)
+        ->  dense dgrad (tcgen05) -> unpool+ReLU mask -> conv2 wgrad / dgrad (tcgen05) -> conv1 wgrad
+  comm: per bucket ONE kernel = NVLink allreduce + 1/size + Adam + bf16 weight refresh; the dense
+        bucket's kernel runs on a second stream underneath the convolution backward.
+
+All persistent state (fp32 master weights, Adam moments, two gradient buffers, bf16 working
+weights, step counter, hyper-parameters, loss ring) lives in symmetric peer-mapped segments.
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Dict, List, Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from ..ops import kernels as K
+from ..parallel import autoselect
+from ..parallel import collectives as C
+from ..parallel.arena import SymmetricArena
+from ..parallel.buckets import plan_arena_buckets
+from ..parallel.optimizer import Adam, DistributedAdam
+from ..runtime import world as _w
+from ..train.engine import Engine, StepResult, _as_dist_adam
+from .spec import ModelSpec, get_spec, init_flat
+
+bf16 = torch.bfloat16
+RING = 1024
+CTRL_STEP, CTRL_HYPER, CTRL_EVAL_LOSS, CTRL_EVAL_CORRECT, CTRL_LOSS_RING, CTRL_CORRECT_RING = 0, 16, 64, 80, 256, 256 + RING * 4
+CTRL_BYTES = 256 + RING * 8
+
+
+class _LazyScalar:
+    """Device scalar read on demand (keeps the training loop free of per-step syncs)."""
+
+    def __init__(self, t: torch.Tensor, scale: float = 1.0):
+        self.t, self.scale, self._v = t, scale, None
+
+    def _get(self):
+        if self._v is None:
+            self._v = self.t.item() * self.scale
+            self.t = None
+        return self._v
+
+    def __float__(self):
+        return float(self._get())
+
+    def __int__(self):
+        return int(self._get())
+
+    def item(self):
+        return self._get()
+
+
+def _env_flag(name: str, default: str = "1") -> bool:
+    return os.environ.get(name, default) not in ("0", "false", "no")
+
+
+class B200Engine(Engine):
+    def __init__(self, spec: Optional[ModelSpec] = None, optimizer=None, *, seed: int = 0, batch_size: int = 128,
+                 use_graph: Optional[bool] = None, dropout: bool = True, use_tc: Optional[bool] = None,
+                 comm_blocks: int = 32, arena: Optional[SymmetricArena] = None, **_ignored):
+        self.spec = spec or get_spec()
+        if self.spec.arch != "mnist_cnn":
+            raise NotImplementedError(f"B200Engine implements the mnist_cnn family; use engine='torch' for {self.spec.arch}")
+        if not torch.cuda.is_available():
+            raise RuntimeError("B200Engine needs a CUDA device")
+        K.lib()                                     # fail loudly if the extension is missing
+        self.device = _w.world().device if _w.is_initialized() and _w.world().is_cuda else torch.device("cuda", torch.cuda.current_device())
+        self.seed = seed
+        self.cap = int(batch_size)
+        self.dropout = dropout
+        self.use_graph = _env_flag("B200DP_GRAPH") if use_graph is None else use_graph
+        tc = _env_flag("B200DP_TC") if use_tc is None else use_tc
+        self.tc_dense = tc and _env_flag("B200DP_TC_DENSE")
+        self.tc_conv = tc and _env_flag("B200DP_TC_CONV")
+        self.comm_blocks = comm_blocks
+        self.global_step = 0
+        self.launches_per_step = 0
+
+        L = self.spec.layers
+        self.C1 = L[0].args["cout"]
+        self.C2 = L[2].args["cout"]
+        self.D = L[5].args["units"]
+        self.F = 7 * 7 * self.C2
+        self.NC = self.spec.num_classes
+        self.drop_rate = L[6].args["rate"]
+        if self.tc_conv and (self.C1 % 32 or self.C2 % 64):
+            self.tc_conv = False
+        if self.tc_dense and (self.F % 8 or self.D % 64):
+            self.tc_dense = False
+
+        # ---- symmetric state -------------------------------------------------------------
+        w = _w.world() if _w.is_initialized() else None
+        if arena is not None:
+            self.arena = arena
+        elif w is not None and w.arena is not None:
+            self.arena = w.arena
+        else:
+            self.arena = self._solo_arena()
+        self.n = self.arena.n
+        self.rank = self.arena.rank
+        T = self.spec.total
+        self.T = T
+        a = self.arena
+        self.seg_ctrl = a.alloc(CTRL_BYTES)
+        self.seg_state = a.alloc(T * 4 * 3)
+        self.seg_grad = a.alloc(T * 4 * 3 + (1 << 16))       # parity 0, parity 1, adasum pong, adasum scratch
+        self.seg_w16 = a.alloc(T * 2)
+        self.master = a.view(self.seg_state, 0, T, torch.float32)
+        self.m = a.view(self.seg_state, T * 4, T, torch.float32)
+        self.v = a.view(self.seg_state, 2 * T * 4, T, torch.float32)
+        self.grads = [a.view(self.seg_grad, p * T * 4, T, torch.float32) for p in (0, 1)]
+        self.w16 = a.view(self.seg_w16, 0, T, bf16)
+        self.step_dev = a.view(self.seg_ctrl, CTRL_STEP, 1, torch.int32)
+        self.hyper_dev = a.view(self.seg_ctrl, CTRL_HYPER, 5, torch.float64)
+        self.eval_loss = a.view(self.seg_ctrl, CTRL_EVAL_LOSS, 1, torch.float32)
+        self.eval_correct = a.view(self.seg_ctrl, CTRL_EVAL_CORRECT, 1, torch.int32)
+        self.loss_ring = a.view(self.seg_ctrl, CTRL_LOSS_RING, RING, torch.float32)
+        self.correct_ring = a.view(self.seg_ctrl, CTRL_CORRECT_RING, RING, torch.int32)
+
+        self.master.copy_(init_flat(self.spec, seed, "cpu").to(self.device))
+        K.cast_f32_to_bf16(self.master, self.w16)
+        self._sharded_ranges: List[Tuple[int, int]] = []
+
+        # ---- activations (plain device memory) --------------------------------------------
+        B, dev = self.cap, self.device
+        e = lambda *s, dt=bf16: torch.empty(*s, device=dev, dtype=dt)
+        self.x = torch.zeros(B, 784, device=dev)
+        self.y = torch.zeros(B, device=dev, dtype=torch.int32)
+        self.a1, self.am1 = e(B, 14, 14, self.C1), e(B, 14, 14, self.C1, dt=torch.uint8)
+        self.c2 = None if self.tc_conv else e(B, 14, 14, self.C2)
+        self.a2, self.am2 = e(B, 7, 7, self.C2), e(B, 7, 7, self.C2, dt=torch.uint8)
+        self.z = torch.zeros(B, self.D, device=dev)
+        self.h, self.dz = e(B, self.D), e(B, self.D)
+        self.dlogits, self.logits = e(B, self.NC, dt=torch.float32), e(B, self.NC, dt=torch.float32)
+        self.dpool, self.dy2, self.da1 = e(B, 7, 7, self.C2), e(B, 14, 14, self.C2), e(B, 14, 14, self.C1)
+        self._pinned = [(torch.empty(B, 784).pin_memory(), torch.empty(B, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+                        for _ in range(3)]
+        self._pin_i = 0
+        self.comm_stream = torch.cuda.Stream(device=dev)
+        self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
+        self._warm: set = set()
+        self.dist: Optional[DistributedAdam] = None
+        self.adam: Optional[Adam] = None
+        self.set_optimizer(optimizer)
+        torch.cuda.synchronize()
+
+    def _solo_arena(self) -> SymmetricArena:
+        import ctypes
+        h = ctypes.c_void_p()
+        K.check(K.lib().b200_comm_create(0, 1, 0, ctypes.byref(h)), "comm_create")
+        return SymmetricArena(h, 0, 1, False, self.device)
+
+    # ------------------------------------------------------------------------------------
+    def pv(self, name: str, buf: torch.Tensor) -> torch.Tensor:
+        p = self.spec.param(name)
+        return buf[p.offset:p.offset + p.numel].view(p.shape)
+
+    def set_optimizer(self, optimizer) -> None:
+        self.dist = _as_dist_adam(optimizer)
+        self.adam = self.dist.base if self.dist else (optimizer if isinstance(optimizer, Adam) else None)
+        if self.adam is not None:
+            a = self.adam
+            self.hyper_dev.copy_(torch.tensor([a.lr, a.beta1, a.beta2, a.epsilon, 0.0 if a.eps_mode == "tf" else 1.0],
+                                              dtype=torch.float64))
+        self._graphs.clear()
+        self._plan_comm()
+
+    def _plan_comm(self) -> None:
+        """Static bucket plan: which ranges each comm kernel reduces, and with which algorithm."""
+        buckets = plan_arena_buckets(self.spec, [["dense.bias", "out."], ["dense.kernel"], ["conv1.", "conv2."]])
+        self.reduce = bool(self.dist is not None and self.n > 1)
+        adasum = self.reduce and self.dist.op is C.Adasum
+        forced = self.dist.algo if self.dist else None
+        self._sharded_ranges = []
+
+        def rng(b):
+            algo = autoselect.choose(b.numel * 4, self.n, forced) if (self.reduce and not adasum) else 0
+            if algo == autoselect.TWOSHOT:
+                self._sharded_ranges.append((b.start, b.numel))
+            return (b.start, b.numel, algo, 1)
+        by = {b.name: b for b in buckets}
+        self.comm_dense = [rng(by["dense.kernel"])]
+        self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1.+conv2."])]
+        self.adasum = adasum
+        self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
+
+    # ------------------------------------------------------------------------------------ kernels
+    def _forward(self, B: int, training: bool) -> None:
+        w = self.w16
+        x, a1, am1, a2, am2 = self.x[:B], self.a1[:B], self.am1[:B], self.a2[:B], self.am2[:B]
+        K.conv1_pool_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1, am1,
+                         self.step_dev if training else None, bump_step=training,
+                         loss_ring=self.loss_ring if training else None, correct_ring=self.correct_ring if training else None)
+        k2, b2 = self.pv("conv2.kernel", w), self.pv("conv2.bias", w)
+        if self.tc_conv:
+            K.conv_tc_fwd(a1, k2, b2, a2, am2, relu=True, pool=True)
+        else:
+            K.conv_direct_fwd(a1, k2, b2, self.c2[:B], 2, relu=True)
+            K.maxpool_fwd(self.c2[:B], a2, am2)
+        a2f = a2.view(B, self.F)
+        wd = self.pv("dense.kernel", w)
+        if self.tc_dense:
+            split = max(1, min(self.F // 64, (148 * 2) // max(1, (self.D // 64) * ((B + 127) // 128))))
+            K.gemm_tc(a2f, wd, self.z[:B], B, self.D, self.F, b_mn_major=True, out_mode=2, split_k=split, block_n=64)
+        else:
+            K.gemm_simple(a2f, wd, self.z[:B], B, self.D, self.F)
+
+    def _head(self, B: int, training: bool) -> None:
+        w = self.w16
+        if training:
+            K.head_fwd_bwd(self.z[:B], self.pv("dense.bias", w), self.pv("out.kernel", w), self.pv("out.bias", w), self.y[:B],
+                           self.h[:B], self.dz[:B], self.dlogits[:B], None, self.loss_ring, self.correct_ring,
+                           drop_rate=self.drop_rate if self.dropout else 0.0, training=True, seed=self.seed,
+                           step_ptr=self.step_dev, zero_z=True, ring=RING)
+        else:
+            K.head_fwd_bwd(self.z[:B], self.pv("dense.bias", w), self.pv("out.kernel", w), self.pv("out.bias", w), self.y[:B],
+                           self.h[:B], None, None, self.logits[:B], self.eval_loss, self.eval_correct,
+                           drop_rate=0.0, training=False, seed=self.seed, step_ptr=None, zero_z=True, ring=0)
+
+    def _backward_and_update(self, B: int, par: int) -> None:
+        w, g = self.w16, self.grads[par]
+        main = torch.cuda.current_stream()
+        K.head_wgrad(self.h[:B], self.dz[:B], self.dlogits[:B], self.pv("out.kernel", g), self.pv("out.bias", g), self.pv("dense.bias", g))
+        a2f = self.a2[:B].view(B, self.F)
+        gd = self.pv("dense.kernel", g)
+        wd = self.pv("dense.kernel", w)
+        dpool = self.dpool[:B].view(B, self.F)
+        if self.tc_dense:
+            K.gemm_tc(a2f, self.dz[:B], gd, self.F, self.D, B, a_mn_major=True, b_mn_major=True, out_mode=0, block_n=128)
+            K.gemm_tc(self.dz[:B], wd, dpool, B, self.F, self.D, out_mode=1, block_n=32)
+        else:
+            K.gemm_simple(a2f, self.dz[:B], gd, self.F, self.D, B, transA=True)
+            K.gemm_simple(self.dz[:B], wd, dpool, B, self.F, self.D, transB=True)
+        # dense bucket: gradient complete and W no longer read -> reduce+update underneath the conv backward
+        ev = torch.cuda.Event()
+        ev.record(main)
+        if not self.adasum:
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                self._comm(0, self.comm_dense, par)
+            ev_done = torch.cuda.Event()
+            ev_done.record(self.comm_stream)
+        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B])
+        k2 = self.pv("conv2.kernel", w)
+        if self.tc_conv:
+            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), self.pv("conv2.bias", g))
+            K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B])
+        else:
+            K.conv_direct_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), self.pv("conv2.bias", g), 2)
+            K.conv_direct_dgrad(self.dy2[:B], k2, self.da1[:B], 2)
+        K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        if self.adasum:
+            self._adasum_update(par)
+        else:
+            self._comm(1, self.comm_rest, par)
+            main.wait_event(ev_done)
+
+    def _comm(self, channel: int, ranges, par: int, *, reduce: Optional[bool] = None, grad_off: Optional[int] = None,
+              scale: Optional[float] = None) -> None:
+        T4 = self.T * 4
+        nb = self.comm_blocks if sum(r[1] for r in ranges) >= (1 << 20) else 8
+        self.arena.fused_allreduce_adam(
+            channel=channel, nblocks=nb, nthreads=512, reduce=self.reduce if reduce is None else reduce,
+            grad_seg=self.seg_grad, grad_cur_off=par * T4 if grad_off is None else grad_off, grad_other_off=(1 - par) * T4,
+            state_seg=self.seg_state, master_off=0, m_off=T4, v_off=2 * T4, w16_seg=self.seg_w16, w16_off=0,
+            ctrl_seg=self.seg_ctrl, step_off=CTRL_STEP, hyper_off=CTRL_HYPER,
+            scale=self.scale if scale is None else scale, ranges=ranges)
+
+    def _adasum_update(self, par: int) -> None:
+        T4 = self.T * 4
+        segs = self.spec.segments()
+        res = self.arena.adasum_levels(self.seg_grad, par * T4, 2 * T4, 3 * T4, [s for s, _ in segs], [n for _, n in segs],
+                                       nblocks=16)
+        # Every rank has passed this step's first level barrier, hence finished reading the previous
+        # step's buffers: the other-parity buffer can be cleared for the next accumulation now.
+        self.grads[1 - par].zero_()
+        ranges = [(r[0], r[1], 0, 0) for r in self.comm_dense + self.comm_rest]
+        self._comm(0, ranges, par, reduce=False, grad_off=res, scale=1.0)
+
+    def _train_graphable(self, B: int, par: int) -> None:
+        c0 = K.LAUNCHES[0]
+        self._forward(B, True)
+        self._head(B, True)
+        self._backward_and_update(B, par)
+        self.launches_per_step = K.LAUNCHES[0] - c0
+
+    # ------------------------------------------------------------------------------------ public
+    def _stage_inputs(self, x, y, B: int) -> None:
+        if isinstance(x, torch.Tensor) and x.is_cuda:
+            self.x[:B].copy_(x.reshape(B, 784), non_blocking=True)
+            self.y[:B].copy_(y.reshape(B).to(torch.int32), non_blocking=True)
+            return
+        if isinstance(x, torch.Tensor) and isinstance(y, torch.Tensor) and x.is_pinned() and y.is_pinned() \
+                and x.dtype == torch.float32 and y.dtype == torch.int32:
+            # caller-owned pinned batches go straight over PCIe (caller keeps them alive until the step ran)
+            self.x[:B].copy_(x.reshape(B, 784), non_blocking=True)
+            self.y[:B].copy_(y.reshape(B), non_blocking=True)
+            return
+        px, py, ev = self._pinned[self._pin_i]
+        self._pin_i = (self._pin_i + 1) % len(self._pinned)
+        ev.synchronize()
+        xs = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
+        ys = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y))
+        px[:B].copy_(xs.reshape(B, 784))
+        py[:B].copy_(ys.reshape(B))
+        self.x[:B].copy_(px[:B], non_blocking=True)
+        self.y[:B].copy_(py[:B], non_blocking=True)
+        ev.record()
+
+    def train_step(self, x, y) -> StepResult:
+        if self.adam is None:
+            raise RuntimeError("no optimizer set; pass optimizer=Adam(...) or compile() the model")
+        B = int(x.shape[0])
+        if B > self.cap:
+            raise ValueError(f"batch {B} exceeds the engine's batch_size={self.cap}")
+        self._stage_inputs(x, y, B)
+        par = self.global_step & 1
+        key = (B, par)
+        if self.use_graph and key in self._warm:
+            g = self._graphs.get(key)
+            if g is None:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._train_graphable(B, par)
+                self._graphs[key] = g
+                # capture does not execute: the step still has to run
+            g.replay()
+        else:
+            self._train_graphable(B, par)
+            self._warm.add(key)
+        self.global_step += 1
+        slot = self.global_step % RING
+        return StepResult(_LazyScalar(self._ring_read(slot, True)), _LazyScalar(self._ring_read(slot, False)), B)
+
+    def _ring_read(self, slot: int, loss: bool) -> torch.Tensor:
+        # a view: valid until the ring wraps (RING steps), which is far longer than any logging cadence
+        return (self.loss_ring if loss else self.correct_ring)[slot]
+
+    def train_step_device(self, B: Optional[int] = None) -> None:
+        """Run a step on whatever is already in ``self.x`` / ``self.y`` (bench: kernel-only timing)."""
+        B = B or self.cap
+        par = self.global_step & 1
+        key = (B, par)
+        if self.use_graph and key in self._warm:
+            g = self._graphs.get(key)
+            if g is None:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._train_graphable(B, par)
+                self._graphs[key] = g
+            g.replay()
+        else:
+            self._train_graphable(B, par)
+            self._warm.add(key)
+        self.global_step += 1
+
+    @torch.no_grad()
+    def eval_batch(self, x, y) -> StepResult:
+        n = int(x.shape[0])
+        self.eval_loss.zero_()
+        self.eval_correct.zero_()
+        for i in range(0, n, self.cap):
+            B = min(self.cap, n - i)
+            self._stage_inputs(x[i:i + B], y[i:i + B], B)
+            self._forward(B, False)
+            self._head(B, False)
+        return StepResult(_LazyScalar(self.eval_loss.clone(), 1.0 / n), _LazyScalar(self.eval_correct.clone()), n)
+
+    @torch.no_grad()
+    def predict(self, x) -> torch.Tensor:
+        n = int(x.shape[0])
+        outs = []
+        dummy = np.zeros(self.cap, np.int32)
+        for i in range(0, n, self.cap):
+            B = min(self.cap, n - i)
+            self._stage_inputs(x[i:i + B], dummy[:B], B)
+            self._forward(B, False)
+            self._head(B, False)
+            outs.append(self.logits[:B].clone())
+        return torch.cat(outs)
+
+    # ------------------------------------------------------------------------------------ state
+    def _gather_sharded(self) -> None:
+        """One-sided: pull every owner's slice of the two-shot ranges into the local fp32 state.
+        Safe between steps: peers cannot start their next update before this rank joins its barrier."""
+        if self.n == 1 or not self._sharded_ranges:
+            return
+        torch.cuda.synchronize()
+        T = self.T
+        for (st, ln) in self._sharded_ranges:
+            chunk = (-(-ln // self.n) + 3) // 4 * 4
+            for r in range(self.n):
+                if r == self.rank:
+                    continue
+                lo, hi = min(r * chunk, ln), min((r + 1) * chunk, ln)
+                if hi <= lo:
+                    continue
+                for base in (0, T, 2 * T):
+                    peer = self.arena.view(self.seg_state, (base + st + lo) * 4, hi - lo, torch.float32, peer=r)
+                    self.arena.view(self.seg_state, (base + st + lo) * 4, hi - lo, torch.float32).copy_(peer)
+        torch.cuda.synchronize()
+
+    def state(self) -> Dict[str, Any]:
+        self._gather_sharded()
+        meta = self.meta()
+        meta.update(global_step=self.global_step, seed=self.seed, engine="b200")
+        if self.adam is not None:
+            a = self.adam
+            meta["optimizer"] = dict(lr=a.lr, beta1=a.beta1, beta2=a.beta2, epsilon=a.epsilon, eps_mode=a.eps_mode)
+        return {"tensors": {"params": self.master.cpu().clone(), "adam_m": self.m.cpu().clone(), "adam_v": self.v.cpu().clone()},
+                "meta": meta}
+
+    def load_state(self, tensors: Dict[str, torch.Tensor], meta: Dict[str, Any]) -> None:
+        if meta.get("arch", self.spec.arch) != self.spec.arch or tensors["params"].numel() != self.T:
+            raise ValueError("checkpoint does not match this model (arch/width differ)")
+        self.master.copy_(tensors["params"].to(self.device))
+        if "adam_m" in tensors:
+            self.m.copy_(tensors["adam_m"].to(self.device))
+            self.v.copy_(tensors["adam_v"].to(self.device))
+        K.cast_f32_to_bf16(self.master, self.w16)
+        self.global_step = int(meta.get("global_step", meta.get("step", 0)))
+        self.step_dev.fill_(self.global_step)
+        if "seed" in meta:
+            self.seed = int(meta["seed"])
+            self._graphs.clear()
+        for gb in self.grads:
+            gb.zero_()
+        torch.cuda.synchronize()
+
+    def broadcast_state(self, root_rank: int = 0) -> None:
+        if not _w.is_initialized() or self.n == 1:
+            return
+        if self.rank == root_rank:
+            self._gather_sharded()
+        else:
+            torch.cuda.synchronize()
+        for t in (self.master, self.m, self.v):
+            C.broadcast_(t, root_rank)
+        K.cast_f32_to_bf16(self.master, self.w16)
+        step, seed = C.broadcast_object((self.global_step, self.seed), root_rank)
+        if seed != self.seed or (step & 1) != (self.global_step & 1):
+            self._graphs.clear()
+        self.global_step, self.seed = step, seed
+        self.step_dev.fill_(self.global_step)
+        torch.cuda.synchronize()
+        _w.barrier()

@@ -1,2 +1,58 @@
-def declare(lib):
-    pass
+"""ctypes prototypes for every entry point in ``include/b200dp.h``."""
+import ctypes as C
+
+P = C.c_void_p
+I = C.c_int
+LL = C.c_longlong
+SZ = C.c_size_t
+F = C.c_float
+D = C.c_double
+U64 = C.c_uint64
+PLL = C.POINTER(C.c_longlong)
+PI = C.POINTER(C.c_int)
+
+_SIGS = {
+    "b200_last_error": (C.c_char_p, []),
+    "b200_comm_pad_bytes": (SZ, []),
+    "b200_comm_create": (I, [I, I, I, C.POINTER(P)]),
+    "b200_comm_set_timeout_ms": (I, [P, D]),
+    "b200_comm_seg_alloc": (I, [P, SZ, PI, P]),
+    "b200_comm_seg_open": (I, [P, I, P]),
+    "b200_comm_seg_ptr": (P, [P, I, I]),
+    "b200_comm_destroy": (I, [P]),
+    "b200_fused_allreduce_adam": (I, [P, I, I, I, I, I, SZ, SZ, I, SZ, SZ, SZ, I, SZ, I, SZ, SZ, F, I, PLL, PLL, PI, PI, P]),
+    "b200_allreduce": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, F, P]),
+    "b200_broadcast": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, P]),
+    "b200_allgather_slices": (I, [P, I, I, I, I, SZ, LL, P]),
+    "b200_adasum_scratch_bytes": (SZ, [I, I]),
+    "b200_adasum_level": (I, [P, I, I, I, I, SZ, I, SZ, I, SZ, I, PLL, PLL, P]),
+    "b200_conv1_pool_fwd": (I, [P, P, P, P, P, I, I, P, I, P, P, I, P]),
+    "b200_conv1_wgrad": (I, [P, P, P, P, P, P, I, I, P]),
+    "b200_head_fwd_bwd": (I, [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, I, U64, P, I, I, I, P]),
+    "b200_head_wgrad": (I, [P, P, P, P, P, P, I, I, I, P]),
+    "b200_unpool_relu_bwd": (I, [P, P, P, P, I, I, I, I, P]),
+    "b200_maxpool_fwd": (I, [P, P, P, I, I, I, I, P]),
+    "b200_conv_direct_fwd": (I, [P, P, P, P, I, I, I, I, I, I, I, I, P]),
+    "b200_conv_direct_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, P]),
+    "b200_conv_direct_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "b200_gemm_simple": (I, [P, P, P, I, I, I, I, I, I, I, P]),
+    "b200_cast_f32_to_bf16": (I, [P, P, LL, P]),
+    "b200_adam_local": (I, [P, P, P, P, P, LL, I, D, D, D, D, I, F, P]),
+    "b200_bias_relu_bf16": (I, [P, P, P, I, I, I, P]),
+    "b200_gemm_tc": (I, [P, P, P, I, I, I, I, I, I, I, I, I, I, I, P]),
+    "b200_conv_tc_fwd": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, P]),
+    "b200_conv_tc_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "b200_conv_tc_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "b200_topology_json": (I, [C.c_char_p, I]),
+    "b200_l2_flush": (I, [P, SZ, P]),
+}
+
+
+def declare(lib) -> None:
+    for name, (res, args) in _SIGS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            continue
+        fn.restype = res
+        fn.argtypes = args

@@ -108,8 +108,9 @@ class TorchEngine(Engine):
 
     def _forward(self, x, training: bool):
         views = self.spec.views(self.params)
+        # dropout counter = 1-based index of the step being run (same convention as the CUDA engine)
         return torch_ref.forward(self.spec, views, x, training=training, seed=self.seed,
-                                 step=self.global_step, dropout=self.dropout,
+                                 step=self.global_step + 1, dropout=self.dropout,
                                  compute_dtype=self.compute_dtype)
 
     def train_step(self, x: ArrayLike, y: ArrayLike) -> StepResult:

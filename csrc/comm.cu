@@ -1,0 +1,676 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch for sm_100a.
+//
+// What this replaces: Horovod's background thread, negotiation,
+// fusion buffer and its MPI/NCCL allreduce/broadcast ops, pulled in by the reference at
+// horovod/Dockerfile:64-65 and driven from horovod/tensorflow_mnist.py:133-143.
+//
+// Design: every rank owns "symmetric segments" (same size, same layout on every rank) whose
+// base pointers are mapped into every peer (CUDA IPC).  A collective is ONE kernel that
+//   1. crosses a flag barrier held in peer memory (st.release.sys / ld.acquire.sys, epochs kept
+//      in device memory so a CUDA-graph replay needs no host-side state),
+//   2. reads the peers' gradient buckets directly over NVLink, sums them in fixed rank order
+//      (bitwise-identical result on every rank),
+//   3. applies the 1/size scale and the Adam update to the fp32 master weights and writes the
+//      bf16 working copy — one-shot: every rank updates everything; two-shot: rank r reduces and
+//      updates slice r only and pushes the updated bf16 slice into every peer.
+// No NCCL, no separate scale/cast/optimizer kernels.
+//
+// "Emulated" communicators place all N ranks' segments on ONE GPU and run the N ranks as
+// blockIdx.y slices of one cooperative launch; this is how the protocol is tested on a single
+// B200 (ranks that wait on one another must never be separate launches on one GPU).
+#include <cooperative_groups.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../include/b200dp.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int MAXR = B200_MAX_RANKS;
+constexpr int MAXCH = B200_MAX_CHANNELS;
+constexpr int MAXB = B200_MAX_COMM_BLOCKS;
+constexpr size_t PAD_FLAGS_BYTES = (size_t)MAXCH * MAXB * MAXR * sizeof(uint32_t);
+constexpr size_t PAD_EPOCH_BYTES = (size_t)MAXCH * MAXB * sizeof(uint32_t);
+constexpr size_t PAD_BYTES = PAD_FLAGS_BYTES + PAD_EPOCH_BYTES;
+
+thread_local std::string g_err;
+
+struct Seg {
+  void* base[MAXR] = {};
+  size_t bytes = 0;
+  bool opened[MAXR] = {};
+};
+
+struct Comm {
+  int rank = 0, n = 1, device = 0;
+  bool emulated = false;
+  std::vector<Seg> segs;
+  unsigned long long timeout_cycles = 40ull * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
+  void* emu_args = nullptr;   // device scratch for per-rank argument blocks (emulated only)
+};
+
+struct PadPtrs {
+  uint32_t* flags[MAXR];   // every rank's flag array (peer-mapped)
+  uint32_t* epochs;        // this rank's epoch counters
+};
+
+// -------------------------------------------------------------------------------------------
+// Flag barrier between the same-index block of every rank.
+// -------------------------------------------------------------------------------------------
+__device__ __forceinline__ void rank_barrier(const PadPtrs& pad, int channel, int bid, int rank, int n,
+                                             uint32_t epoch, unsigned long long timeout) {
+  __syncthreads();
+  if ((int)threadIdx.x < n) {
+    const int peer = threadIdx.x;
+    const size_t slot = ((size_t)channel * MAXB + bid) * MAXR;
+    st_release_sys(pad.flags[peer] + slot + rank, epoch);
+    const uint32_t* mine = pad.flags[rank] + slot + peer;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((unsigned long long)(clock64() - t0) > timeout) {
+        printf("b200dp: collective timeout: rank %d channel %d block %d never saw epoch %u from rank %d (has %u)\n",
+               rank, channel, bid, epoch, peer, ld_acquire_sys(mine));
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+struct Range {
+  long long start;    // elements
+  long long numel;    // multiple of 4
+  int algo;           // 0 one-shot, 1 two-shot
+  int zero_other;     // clear the other-parity gradient buffer over this range
+};
+
+struct FusedArgs {
+  int rank, n, channel;
+  int reduce;                 // 0: gradients are already final locally (single rank / after Adasum)
+  PadPtrs pad;
+  const float* grad[MAXR];    // current-parity gradient buffers of every rank
+  float* grad_other;          // local other-parity buffer
+  float* master;              // local fp32 weights / Adam moments
+  float* m;
+  float* v;
+  bf16* w16[MAXR];            // bf16 working weights of every rank
+  const int* step_ptr;        // device: 1-based step being applied
+  const double* hyper;        // device: lr, beta1, beta2, eps, eps_mode
+  float scale;                // 1/size for Average, 1 for Sum
+  int nranges;
+  Range ranges[B200_MAX_RANGES];
+  unsigned long long timeout;
+};
+
+struct AdamCoef {
+  float b1, b2, eps, step_size, vscale;
+};
+
+__device__ __forceinline__ float adam_elem(float g, float& p, float& m, float& v, const AdamCoef& c) {
+  m = c.b1 * m + (1.f - c.b1) * g;
+  v = c.b2 * v + (1.f - c.b2) * g * g;
+  p -= c.step_size * m / (sqrtf(v) * c.vscale + c.eps);
+  return p;
+}
+
+__device__ __forceinline__ void adam_vec4(const FusedArgs& a, const AdamCoef& c, long long i, float4 g) {
+  float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+  adam_elem(g.x, p.x, m.x, v.x, c);
+  adam_elem(g.y, p.y, m.y, v.y, c);
+  adam_elem(g.z, p.z, m.z, v.z, c);
+  adam_elem(g.w, p.w, m.w, v.w, c);
+  st_f4(a.master + i, p);
+  st_f4(a.m + i, m);
+  st_f4(a.v + i, v);
+}
+
+__device__ __forceinline__ float4 reduce_peers(const FusedArgs& a, long long i) {
+  float4 s = ld_f4(a.grad[0] + i);
+  if (a.reduce) {
+#pragma unroll 1
+    for (int r = 1; r < a.n; ++r) {
+      const float4 t = ld_f4(a.grad[r] + i);
+      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+    }
+  }
+  s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
+  return s;
+}
+
+template <bool EMU>
+__global__ void __launch_bounds__(512) fused_allreduce_adam_kernel(const FusedArgs areal, const FusedArgs* aemu) {
+  const FusedArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x;
+  const long long nthr = (long long)gridDim.x * blockDim.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  const bool multi = a.n > 1 && a.reduce;
+
+  __shared__ AdamCoef coef;
+  if (threadIdx.x == 0) {
+    const int t = *a.step_ptr;
+    const double lr = a.hyper[0], b1 = a.hyper[1], b2 = a.hyper[2], eps = a.hyper[3];
+    const double bc1 = 1.0 - pow(b1, (double)t), bc2 = 1.0 - pow(b2, (double)t);
+    coef.b1 = (float)b1;
+    coef.b2 = (float)b2;
+    coef.eps = (float)eps;
+    if (a.hyper[4] == 0.0) {            // TF placement: lr_t * m / (sqrt(v) + eps)
+      coef.step_size = (float)(lr * sqrt(bc2) / bc1);
+      coef.vscale = 1.f;
+    } else {                            // torch placement: lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps)
+      coef.step_size = (float)(lr / bc1);
+      coef.vscale = (float)(1.0 / sqrt(bc2));
+    }
+  }
+  if (multi) rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  else __syncthreads();
+  const AdamCoef c = coef;
+
+  bool any_twoshot = false;
+  for (int ri = 0; ri < a.nranges; ++ri) {
+    const Range rg = a.ranges[ri];
+    if (rg.algo == 0 || !multi) {
+      // one-shot: every rank reduces and updates the whole range
+      for (long long q = tid; q < rg.numel / 4; q += nthr) {
+        const long long i = rg.start + q * 4;
+        const float4 g = reduce_peers(a, i);
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        *reinterpret_cast<uint2*>(a.w16[a.rank] + i) = pack_bf16x4(p);
+        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(0.f, 0.f, 0.f, 0.f));
+      }
+    } else {
+      // two-shot: reduce + update the owned slice, push the bf16 result to every rank
+      any_twoshot = true;
+      long long chunk = (rg.numel + a.n - 1) / a.n;
+      chunk = (chunk + 3) / 4 * 4;
+      const long long lo = min((long long)a.rank * chunk, rg.numel);
+      const long long hi = min(lo + chunk, rg.numel);
+      for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
+        const long long i = rg.start + lo + q * 4;
+        const float4 g = reduce_peers(a, i);
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        const uint2 w = pack_bf16x4(p);
+#pragma unroll 1
+        for (int r = 0; r < a.n; ++r) *reinterpret_cast<uint2*>(a.w16[r] + i) = w;
+      }
+      if (rg.zero_other)
+        for (long long q = tid; q < rg.numel / 4; q += nthr)
+          st_f4(a.grad_other + rg.start + q * 4, make_float4(0.f, 0.f, 0.f, 0.f));
+    }
+  }
+  if (any_twoshot) {
+    __threadfence_system();
+    rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  }
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+}
+
+// -------------------------------------------------------------------------------------------
+// Plain allreduce / broadcast / all-gather on staging buffers (public hvd.allreduce/broadcast).
+// -------------------------------------------------------------------------------------------
+struct PlainArgs {
+  int rank, n, channel, algo, root;
+  PadPtrs pad;
+  const float* src[MAXR];
+  float* dst[MAXR];
+  long long numel;            // multiple of 4
+  float scale;
+  unsigned long long timeout;
+};
+
+template <bool EMU>
+__global__ void __launch_bounds__(512) allreduce_plain_kernel(const PlainArgs areal, const PlainArgs* aemu) {
+  const PlainArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (a.algo == 0) {
+    for (long long q = tid; q < a.numel / 4; q += nthr) {
+      float4 s = ld_f4(a.src[0] + q * 4);
+      for (int r = 1; r < a.n; ++r) {
+        const float4 t = ld_f4(a.src[r] + q * 4);
+        s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+      }
+      s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
+      st_f4(a.dst[a.rank] + q * 4, s);
+    }
+  } else {
+    long long chunk = (a.numel + a.n - 1) / a.n;
+    chunk = (chunk + 3) / 4 * 4;
+    const long long lo = min((long long)a.rank * chunk, a.numel), hi = min(lo + chunk, a.numel);
+    for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
+      const long long i = lo + q * 4;
+      float4 s = ld_f4(a.src[0] + i);
+      for (int r = 1; r < a.n; ++r) {
+        const float4 t = ld_f4(a.src[r] + i);
+        s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+      }
+      s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
+      for (int r = 0; r < a.n; ++r) st_f4(a.dst[r] + i, s);
+    }
+    __threadfence_system();
+    rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  }
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+}
+
+// mode 0: broadcast src[root] -> dst[rank];  mode 1: in-place all-gather of rank-owned slices of dst
+template <bool EMU>
+__global__ void __launch_bounds__(512) copy_collective_kernel(const PlainArgs areal, const PlainArgs* aemu, int mode) {
+  const PlainArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (mode == 0) {
+    if (a.rank != a.root || a.src[a.root] != a.dst[a.rank])
+      for (long long q = tid; q < a.numel / 4; q += nthr) st_f4(a.dst[a.rank] + q * 4, ld_f4(a.src[a.root] + q * 4));
+  } else {
+    long long chunk = (a.numel + a.n - 1) / a.n;
+    chunk = (chunk + 3) / 4 * 4;
+    for (int r = 0; r < a.n; ++r) {
+      if (r == a.rank) continue;
+      const long long lo = min((long long)r * chunk, a.numel), hi = min(lo + chunk, a.numel);
+      for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
+        const long long i = lo + q * 4;
+        st_f4(a.dst[a.rank] + i, ld_f4(a.dst[r] + i));
+      }
+    }
+  }
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+}
+
+// -------------------------------------------------------------------------------------------
+// Adasum: log2(N) levels; at level L rank r pairs with r ^ (1<<L).
+//   a' = (1 - a.b/(2|a|^2)) a + (1 - a.b/(2|b|^2)) b      per tensor segment
+// "a" is always the lower rank's vector so both partners compute bit-identical results.
+// Kernel 1 writes per-block partial dot products (fixed block->element mapping), kernel 2 sums
+// the partials in block order and combines — deterministic, no atomics.
+// -------------------------------------------------------------------------------------------
+struct AdasumArgs {
+  int rank, n, channel, level;
+  PadPtrs pad;
+  const float* cur[MAXR];     // level-input vectors of every rank
+  float* next;                // local level-output vector
+  double* partials;           // local scratch [gridDim.x][nseg][3]
+  int nseg;
+  long long seg_start[B200_MAX_SEGMENTS];
+  long long seg_numel[B200_MAX_SEGMENTS];
+  unsigned long long timeout;
+};
+
+template <bool EMU>
+__global__ void __launch_bounds__(256) adasum_dots_kernel(const AdasumArgs areal, const AdasumArgs* aemu) {
+  const AdasumArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+  const int partner = a.rank ^ (1 << a.level);
+  const float* va = a.cur[min(a.rank, partner)];
+  const float* vb = a.cur[max(a.rank, partner)];
+  __shared__ double red[3][8];
+  for (int s = 0; s < a.nseg; ++s) {
+    double dab = 0, daa = 0, dbb = 0;
+    const float* pa = va + a.seg_start[s];
+    const float* pb = vb + a.seg_start[s];
+    for (long long i = (long long)bid * blockDim.x + threadIdx.x; i < a.seg_numel[s]; i += (long long)gridDim.x * blockDim.x) {
+      const double x = pa[i], y = pb[i];
+      dab += x * y; daa += x * x; dbb += y * y;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      dab += __shfl_xor_sync(0xffffffffu, dab, o);
+      daa += __shfl_xor_sync(0xffffffffu, daa, o);
+      dbb += __shfl_xor_sync(0xffffffffu, dbb, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { red[0][w] = dab; red[1][w] = daa; red[2][w] = dbb; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      double t = 0;
+      for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += red[threadIdx.x][k];
+      a.partials[((size_t)bid * a.nseg + s) * 3 + threadIdx.x] = t;
+    }
+    __syncthreads();
+  }
+}
+
+template <bool EMU>
+__global__ void __launch_bounds__(256) adasum_combine_kernel(const AdasumArgs areal, const AdasumArgs* aemu, int nblk_dots) {
+  const AdasumArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int partner = a.rank ^ (1 << a.level);
+  const float* va = a.cur[min(a.rank, partner)];
+  const float* vb = a.cur[max(a.rank, partner)];
+  __shared__ float ca_s[B200_MAX_SEGMENTS], cb_s[B200_MAX_SEGMENTS];
+  if ((int)threadIdx.x < a.nseg) {
+    double dab = 0, daa = 0, dbb = 0;
+    for (int b = 0; b < nblk_dots; ++b) {
+      const double* p = a.partials + ((size_t)b * a.nseg + threadIdx.x) * 3;
+      dab += p[0]; daa += p[1]; dbb += p[2];
+    }
+    ca_s[threadIdx.x] = (float)(1.0 - (daa > 0 ? dab / (2.0 * daa) : 0.0));
+    cb_s[threadIdx.x] = (float)(1.0 - (dbb > 0 ? dab / (2.0 * dbb) : 0.0));
+  }
+  __syncthreads();
+  for (int s = 0; s < a.nseg; ++s) {
+    const float ca = ca_s[s], cb = cb_s[s];
+    const long long st = a.seg_start[s];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.seg_numel[s]; i += (long long)gridDim.x * blockDim.x)
+      a.next[st + i] = ca * va[st + i] + cb * vb[st + i];
+  }
+}
+
+// -------------------------------------------------------------------------------------------
+int check_seg(Comm* c, int seg, size_t off, size_t bytes, const char* what) {
+  B200_REQUIRE(seg >= 0 && seg < (int)c->segs.size(), "%s: segment %d does not exist", what, seg);
+  B200_REQUIRE(off + bytes <= c->segs[seg].bytes, "%s: [%zu, %zu) outside segment %d of %zu bytes", what, off, off + bytes, seg, c->segs[seg].bytes);
+  B200_REQUIRE(off % 16 == 0, "%s: offset %zu not 16-byte aligned", what, off);
+  return B200_OK;
+}
+
+inline char* seg_ptr(Comm* c, int seg, int peer, size_t off) { return (char*)c->segs[seg].base[peer] + off; }
+
+void fill_pad(Comm* c, int as_rank, PadPtrs* p) {
+  for (int r = 0; r < c->n; ++r) p->flags[r] = (uint32_t*)seg_ptr(c, 0, r, 0);
+  p->epochs = (uint32_t*)seg_ptr(c, 0, as_rank, PAD_FLAGS_BYTES);
+}
+
+template <typename Args, typename KReal, typename KEmu, typename... Extra>
+int launch_ranked(Comm* c, Args* per_rank, KReal kreal, KEmu kemu, int nblocks, int nthreads, cudaStream_t st, Extra... extra) {
+  if (!c->emulated) {
+    kreal<<<nblocks, nthreads, 0, st>>>(per_rank[0], nullptr, extra...);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
+  B200_REQUIRE(sizeof(Args) * c->n <= 65536, "argument block too large");
+  B200_CHECK(cudaMemcpyAsync(c->emu_args, per_rank, sizeof(Args) * c->n, cudaMemcpyHostToDevice, st));
+  const Args* dev = (const Args*)c->emu_args;
+  Args dummy = per_rank[0];
+  void* params[] = {(void*)&dummy, (void*)&dev, (void*)&extra...};
+  B200_CHECK(cudaLaunchCooperativeKernel((void*)kemu, dim3(nblocks, c->n), dim3(nthreads), params, 0, st));
+  // per_rank is host stack memory: the async copy above must finish before we return
+  B200_CHECK(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+}  // namespace
+
+void b200_set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+
+extern "C" {
+
+const char* b200_last_error(void) { return g_err.c_str(); }
+
+size_t b200_comm_pad_bytes(void) { return PAD_BYTES; }
+
+int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out) {
+  B200_REQUIRE(nranks >= 1 && nranks <= MAXR, "nranks %d outside [1, %d]", nranks, MAXR);
+  B200_REQUIRE(rank >= 0 && rank < nranks, "rank %d outside world of %d", rank, nranks);
+  Comm* c = new Comm;
+  c->rank = emulated ? 0 : rank;
+  c->n = nranks;
+  c->emulated = emulated != 0;
+  B200_CHECK(cudaGetDevice(&c->device));
+  if (c->emulated) B200_CHECK(cudaMalloc(&c->emu_args, 65536));
+  *out = c;
+  return B200_OK;
+}
+
+int b200_comm_set_timeout_ms(b200_comm_t h, double ms) {
+  Comm* c = (Comm*)h;
+  int khz = 0;
+  B200_CHECK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device));
+  c->timeout_cycles = (unsigned long long)(ms * (double)khz);
+  return B200_OK;
+}
+
+// Allocates the local part of a new symmetric segment (zero-filled). Returns its id and, for real
+// communicators, the 64-byte CUDA IPC handle to hand to the peers. Segment 0 must be the signal
+// pad (b200_comm_pad_bytes()).
+int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(bytes > 0 && bytes % 256 == 0, "segment size %zu must be a positive multiple of 256", bytes);
+  B200_REQUIRE(!c->segs.empty() || bytes >= PAD_BYTES, "segment 0 is the signal pad and needs >= %zu bytes", PAD_BYTES);
+  Seg s;
+  s.bytes = bytes;
+  if (c->emulated) {
+    for (int r = 0; r < c->n; ++r) {
+      B200_CHECK(cudaMalloc(&s.base[r], bytes));
+      B200_CHECK(cudaMemset(s.base[r], 0, bytes));
+    }
+  } else {
+    B200_CHECK(cudaMalloc(&s.base[c->rank], bytes));
+    B200_CHECK(cudaMemset(s.base[c->rank], 0, bytes));
+    if (ipc_handle_out && c->n > 1) {
+      cudaIpcMemHandle_t hd;
+      B200_CHECK(cudaIpcGetMemHandle(&hd, s.base[c->rank]));
+      memcpy(ipc_handle_out, &hd, sizeof hd);
+    }
+  }
+  B200_CHECK(cudaDeviceSynchronize());
+  c->segs.push_back(s);
+  *seg_id = (int)c->segs.size() - 1;
+  return B200_OK;
+}
+
+// all_handles: nranks x 64 bytes, rank order (gathered by the caller over its control plane).
+int b200_comm_seg_open(b200_comm_t h, int seg_id, const void* all_handles) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(seg_id >= 0 && seg_id < (int)c->segs.size(), "segment %d does not exist", seg_id);
+  if (c->emulated || c->n == 1) return B200_OK;
+  Seg& s = c->segs[seg_id];
+  for (int r = 0; r < c->n; ++r) {
+    if (r == c->rank || s.opened[r]) continue;
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, (const char*)all_handles + (size_t)r * sizeof hd, sizeof hd);
+    B200_CHECK(cudaIpcOpenMemHandle(&s.base[r], hd, cudaIpcMemLazyEnablePeerAccess));
+    s.opened[r] = true;
+  }
+  return B200_OK;
+}
+
+void* b200_comm_seg_ptr(b200_comm_t h, int seg_id, int peer) {
+  Comm* c = (Comm*)h;
+  if (seg_id < 0 || seg_id >= (int)c->segs.size() || peer < 0 || peer >= c->n) return nullptr;
+  return c->segs[seg_id].base[peer];
+}
+
+int b200_comm_destroy(b200_comm_t h) {
+  Comm* c = (Comm*)h;
+  if (!c) return B200_OK;
+  cudaDeviceSynchronize();
+  for (Seg& s : c->segs)
+    for (int r = 0; r < c->n; ++r) {
+      if (!s.base[r]) continue;
+      if (c->emulated || r == c->rank) cudaFree(s.base[r]);
+      else if (s.opened[r]) cudaIpcCloseMemHandle(s.base[r]);
+    }
+  if (c->emu_args) cudaFree(c->emu_args);
+  delete c;
+  return B200_OK;
+}
+
+// The fused step: allreduce(grad) -> scale -> Adam(master, m, v) -> bf16 weights, per range.
+// All buffers live in symmetric segments and are addressed as (segment, byte offset).
+// In an emulated communicator the call runs every rank (each on its own copy of the segments).
+int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthreads, int reduce,
+                              int grad_seg, size_t grad_cur_off, size_t grad_other_off,
+                              int state_seg, size_t master_off, size_t m_off, size_t v_off,
+                              int w16_seg, size_t w16_off, int ctrl_seg, size_t step_off, size_t hyper_off,
+                              float scale, int nranges, const long long* range_start, const long long* range_numel,
+                              const int* range_algo, const int* range_zero_other, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(channel >= 0 && channel < MAXCH, "channel %d outside [0, %d)", channel, MAXCH);
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB, "nblocks %d outside [1, %d]", nblocks, MAXB);
+  B200_REQUIRE(nthreads >= 32 && nthreads <= 512 && nthreads % 32 == 0, "nthreads %d invalid", nthreads);
+  B200_REQUIRE(nranges >= 1 && nranges <= B200_MAX_RANGES, "nranges %d outside [1, %d]", nranges, B200_MAX_RANGES);
+  long long max_end = 0;
+  for (int i = 0; i < nranges; ++i) {
+    B200_REQUIRE(range_start[i] % 4 == 0 && range_numel[i] % 4 == 0 && range_numel[i] >= 0, "range %d not 4-element aligned", i);
+    max_end = max_end > range_start[i] + range_numel[i] ? max_end : range_start[i] + range_numel[i];
+  }
+  int rc;
+  if ((rc = check_seg(c, grad_seg, grad_cur_off, max_end * 4, "grad"))) return rc;
+  if ((rc = check_seg(c, grad_seg, grad_other_off, max_end * 4, "grad_other"))) return rc;
+  if ((rc = check_seg(c, state_seg, master_off, max_end * 4, "master"))) return rc;
+  if ((rc = check_seg(c, state_seg, m_off, max_end * 4, "adam_m"))) return rc;
+  if ((rc = check_seg(c, state_seg, v_off, max_end * 4, "adam_v"))) return rc;
+  if ((rc = check_seg(c, w16_seg, w16_off, max_end * 2, "w16"))) return rc;
+  if ((rc = check_seg(c, ctrl_seg, step_off, 16, "step"))) return rc;
+  if ((rc = check_seg(c, ctrl_seg, hyper_off, 48, "hyper"))) return rc;
+
+  FusedArgs args[MAXR];
+  const int nr = c->emulated ? c->n : 1;
+  for (int k = 0; k < nr; ++k) {
+    const int me = c->emulated ? k : c->rank;
+    FusedArgs& a = args[k];
+    memset(&a, 0, sizeof a);
+    a.rank = me; a.n = c->n; a.channel = channel; a.reduce = reduce;
+    fill_pad(c, me, &a.pad);
+    for (int r = 0; r < c->n; ++r) {
+      a.grad[r] = (const float*)seg_ptr(c, grad_seg, r, grad_cur_off);
+      a.w16[r] = (bf16*)seg_ptr(c, w16_seg, r, w16_off);
+    }
+    if (!reduce) a.grad[0] = (const float*)seg_ptr(c, grad_seg, me, grad_cur_off);
+    a.grad_other = (float*)seg_ptr(c, grad_seg, me, grad_other_off);
+    a.master = (float*)seg_ptr(c, state_seg, me, master_off);
+    a.m = (float*)seg_ptr(c, state_seg, me, m_off);
+    a.v = (float*)seg_ptr(c, state_seg, me, v_off);
+    a.step_ptr = (const int*)seg_ptr(c, ctrl_seg, me, step_off);
+    a.hyper = (const double*)seg_ptr(c, ctrl_seg, me, hyper_off);
+    a.scale = scale;
+    a.nranges = nranges;
+    for (int i = 0; i < nranges; ++i) a.ranges[i] = Range{range_start[i], range_numel[i], range_algo[i], range_zero_other[i]};
+    a.timeout = c->timeout_cycles;
+  }
+  return launch_ranked(c, args, fused_allreduce_adam_kernel<false>, fused_allreduce_adam_kernel<true>, nblocks, nthreads,
+                       (cudaStream_t)stream);
+}
+
+static int plain_args(Comm* c, PlainArgs* args, int channel, int algo, int root, int src_seg, size_t src_off,
+                      int dst_seg, size_t dst_off, long long numel, float scale) {
+  B200_REQUIRE(channel >= 0 && channel < MAXCH, "channel %d outside [0, %d)", channel, MAXCH);
+  B200_REQUIRE(numel >= 0 && numel % 4 == 0, "numel %lld must be a multiple of 4", numel);
+  B200_REQUIRE(root >= 0 && root < c->n, "root %d outside world of %d", root, c->n);
+  int rc;
+  if ((rc = check_seg(c, src_seg, src_off, numel * 4, "src"))) return rc;
+  if ((rc = check_seg(c, dst_seg, dst_off, numel * 4, "dst"))) return rc;
+  const int nr = c->emulated ? c->n : 1;
+  for (int k = 0; k < nr; ++k) {
+    const int me = c->emulated ? k : c->rank;
+    PlainArgs& a = args[k];
+    memset(&a, 0, sizeof a);
+    a.rank = me; a.n = c->n; a.channel = channel; a.algo = algo; a.root = root;
+    fill_pad(c, me, &a.pad);
+    for (int r = 0; r < c->n; ++r) {
+      a.src[r] = (const float*)seg_ptr(c, src_seg, r, src_off);
+      a.dst[r] = (float*)seg_ptr(c, dst_seg, r, dst_off);
+    }
+    a.numel = numel;
+    a.scale = scale;
+    a.timeout = c->timeout_cycles;
+  }
+  return B200_OK;
+}
+
+// dst = scale * sum_r src_r  (fp32). algo 0 one-shot (dst local), 1 two-shot (dst written on every rank).
+int b200_allreduce(b200_comm_t h, int channel, int nblocks, int nthreads, int algo, int src_seg, size_t src_off,
+                   int dst_seg, size_t dst_off, long long numel, float scale, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  PlainArgs args[MAXR];
+  int rc = plain_args(c, args, channel, algo, 0, src_seg, src_off, dst_seg, dst_off, numel, scale);
+  if (rc) return rc;
+  return launch_ranked(c, args, allreduce_plain_kernel<false>, allreduce_plain_kernel<true>, nblocks, nthreads, (cudaStream_t)stream);
+}
+
+// Every rank copies root's src into its own dst (peer reads over NVLink).
+int b200_broadcast(b200_comm_t h, int channel, int nblocks, int nthreads, int root, int src_seg, size_t src_off,
+                   int dst_seg, size_t dst_off, long long numel, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  PlainArgs args[MAXR];
+  int rc = plain_args(c, args, channel, 0, root, src_seg, src_off, dst_seg, dst_off, numel, 1.f);
+  if (rc) return rc;
+  return launch_ranked(c, args, copy_collective_kernel<false>, copy_collective_kernel<true>, nblocks, nthreads, (cudaStream_t)stream, 0);
+}
+
+// In-place all-gather: rank r owns slice r (same slicing as the two-shot path) of the buffer.
+int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads, int seg, size_t off, long long numel, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  PlainArgs args[MAXR];
+  int rc = plain_args(c, args, channel, 0, 0, seg, off, seg, off, numel, 1.f);
+  if (rc) return rc;
+  return launch_ranked(c, args, copy_collective_kernel<false>, copy_collective_kernel<true>, nblocks, nthreads, (cudaStream_t)stream, 1);
+}
+
+size_t b200_adasum_scratch_bytes(int nblocks, int nseg) { return (size_t)nblocks * nseg * 3 * sizeof(double); }
+
+// One Adasum level: next = combine(cur[lower], cur[higher]) for partner = rank ^ (1 << level).
+// cur/next are (segment, offset) fp32 vectors; scratch is local memory of
+// b200_adasum_scratch_bytes(nblocks, nseg) bytes per rank, addressed the same way.
+int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cur_seg, size_t cur_off, int next_seg,
+                      size_t next_off, int scratch_seg, size_t scratch_off, int nseg, const long long* seg_start,
+                      const long long* seg_numel, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(channel >= 0 && channel < MAXCH, "channel %d outside [0, %d)", channel, MAXCH);
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB, "nblocks %d outside [1, %d]", nblocks, MAXB);
+  B200_REQUIRE((c->n & (c->n - 1)) == 0, "Adasum needs a power-of-two world size, got %d", c->n);
+  B200_REQUIRE(level >= 0 && (1 << level) < c->n, "level %d invalid for %d ranks", level, c->n);
+  B200_REQUIRE(nseg >= 1 && nseg <= B200_MAX_SEGMENTS, "nseg %d outside [1, %d]", nseg, B200_MAX_SEGMENTS);
+  long long max_end = 0;
+  for (int i = 0; i < nseg; ++i) max_end = max_end > seg_start[i] + seg_numel[i] ? max_end : seg_start[i] + seg_numel[i];
+  int rc;
+  if ((rc = check_seg(c, cur_seg, cur_off, max_end * 4, "adasum cur"))) return rc;
+  if ((rc = check_seg(c, next_seg, next_off, max_end * 4, "adasum next"))) return rc;
+  if ((rc = check_seg(c, scratch_seg, scratch_off, b200_adasum_scratch_bytes(nblocks, nseg), "adasum scratch"))) return rc;
+  AdasumArgs args[MAXR];
+  const int nr = c->emulated ? c->n : 1;
+  for (int k = 0; k < nr; ++k) {
+    const int me = c->emulated ? k : c->rank;
+    AdasumArgs& a = args[k];
+    memset(&a, 0, sizeof a);
+    a.rank = me; a.n = c->n; a.channel = channel; a.level = level;
+    fill_pad(c, me, &a.pad);
+    for (int r = 0; r < c->n; ++r) a.cur[r] = (const float*)seg_ptr(c, cur_seg, r, cur_off);
+    a.next = (float*)seg_ptr(c, next_seg, me, next_off);
+    a.partials = (double*)seg_ptr(c, scratch_seg, me, scratch_off);
+    a.nseg = nseg;
+    for (int i = 0; i < nseg; ++i) { a.seg_start[i] = seg_start[i]; a.seg_numel[i] = seg_numel[i]; }
+    a.timeout = c->timeout_cycles;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  rc = launch_ranked(c, args, adasum_dots_kernel<false>, adasum_dots_kernel<true>, nblocks, 256, st);
+  if (rc) return rc;
+  if (!c->emulated) {
+    adasum_combine_kernel<false><<<nblocks * 2, 256, 0, st>>>(args[0], nullptr, nblocks);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
+  // emulated: ranks do not wait on each other inside the combine kernel, so a plain launch is fine
+  adasum_combine_kernel<true><<<dim3(nblocks * 2, c->n), 256, 0, st>>>(args[0], (const AdasumArgs*)c->emu_args, nblocks);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // extern "C"

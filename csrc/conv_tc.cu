@@ -1,0 +1,426 @@
+// Implicit-GEMM convolution on tcgen05 for sm_100a (NHWC bf16, stride 1, SAME padding, W <= 16).
+//
+// No im2col buffer exists anywhere: the filter taps are applied by the TMA unit — for tap (kh,kw) the
+// producer loads the SAME 4-D box {channels, 16, 8, 1} of the activation tensor shifted by (kh-pad, kw-pad),
+// and out-of-bounds rows/columns (the SAME halo, and columns W..15 of the 16-wide tile) arrive as zeros.
+// An M tile is an 8x16 pixel patch of one image (row r = 16*hh + ww), so the 2x2 max-pool partners of a pixel
+// sit in the same warp's TMEM lanes (lane^1, lane^16, lane^17) and pooling is three shuffles in the epilogue.
+//
+//   forward : D[pix, co] = sum_{tap,ci} in[pix + tap, ci] * W[tap, ci, co]      A K-major, B MN-major
+//   dgrad   : D[pix, ci] = sum_{tap,co} dy[pix - tap, co] * W[tap, ci, co]      A K-major, B K-major
+//   wgrad   : D[(tap,ci), co] = sum_pix in[pix + tap, ci] * dy[pix, co]         A MN-major (taps stacked in M), B MN-major
+//
+// Replaces cuDNN's conv2d fwd/dgrad/wgrad behind layers.conv2d (horovod/tensorflow_mnist.py:49-60;
+// horovod/tensorflow_mnist_gpu.py:47-56) — SURVEY §2.5a K5, K6, K13.
+#include "../include/b200dp.h"
+#include "tc_sm100.cuh"
+
+namespace {
+
+using namespace tc;
+
+constexpr int TILE_H = 8, TILE_W = 16, TILE_PIX = 128;
+
+struct ConvParams {
+  int B, H, W, Ci, Co, k, pad;
+  int mode;          // 0 forward, 1 dgrad
+  int KC;            // reduction channels per k-block (32 or 64)
+  int BN;            // output channels per CTA
+  int kc_blocks;     // reduction-channel blocks per tap
+  int relu, pool;
+  const bf16* bias;
+  bf16* out;
+  uint8_t* argmax;
+  int tiles_h;       // ceil(H / 8)
+  uint32_t tmem_cols;
+  int nstage;
+};
+
+__global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB, const ConvParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int a_bytes = TILE_PIX * p.KC * 2;
+  const int b_bytes = p.BN * p.KC * 2;
+  const int stage_bytes = a_bytes + ((b_bytes + 1023) & ~1023);
+  uint64_t* full = (uint64_t*)(smem + p.nstage * stage_bytes);
+  uint64_t* empty = full + p.nstage;
+  uint64_t* tmem_full = empty + p.nstage;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * p.BN;
+  const int img = blockIdx.y / p.tiles_h, h0 = (blockIdx.y % p.tiles_h) * TILE_H;
+  const int nkb = p.k * p.k * p.kc_blocks;
+  const uint32_t swz = p.KC == 64 ? SW_128B : SW_64B;
+  const int row_bytes = p.KC * 2;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < p.nstage; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int tap = kb / p.kc_blocks, cb = kb % p.kc_blocks;
+        const int kh = tap / p.k, kw = tap % p.k;
+        const int dh = p.mode == 0 ? kh - p.pad : p.pad - kh;
+        const int dw = p.mode == 0 ? kw - p.pad : p.pad - kw;
+        mbar_wait(empty + stage, phase ^ 1, 11);
+        uint8_t* sA = smem + stage * stage_bytes;
+        uint8_t* sB = sA + a_bytes;
+        mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + b_bytes));
+        tma_load_4d(sA, &tmA, full + stage, cb * p.KC, dw, h0 + dh, img);
+        if (p.mode == 0) {
+          // rows = (tap, ci) block, cols = co: MN-major B, one 64-column box per 64 output channels
+          for (int j = 0; j < p.BN / 64; ++j)
+            tma_load_2d(sB + j * (p.KC * 128), &tmB, full + stage, n0 + 64 * j, tap * p.Ci + cb * p.KC);
+        } else {
+          // rows = ci (this CTA's N), cols = co block: K-major B
+          tma_load_2d(sB, &tmB, full + stage, cb * p.KC, tap * p.Ci + n0);
+        }
+        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.BN, 0, p.mode == 0 ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(full + stage, phase, 12);
+        tc_fence_after();
+        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
+        const uint32_t sB = sA + a_bytes;
+        for (int ks = 0; ks < p.KC / 16; ++ks) {
+          const uint64_t ad = make_smem_desc(sA + ks * 32, 16, 8 * row_bytes, swz);
+          const uint64_t bd = p.mode == 0 ? make_smem_desc(sB + ks * 2048, p.KC * 128, 1024, SW_128B)
+                                          : make_smem_desc(sB + ks * 32, 16, 8 * row_bytes, swz);
+          umma_bf16(tmem_base, ad, bd, idesc, (kb > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit(empty + stage);
+        if (kb == nkb - 1) umma_commit(tmem_full);
+        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    mbar_wait(tmem_full, 0, 13);
+    tc_fence_after();
+    const int q = warp & 3;
+    const int hh = 2 * q + (lane >> 4), ww = lane & 15;
+    const int h = h0 + hh;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int Cout = p.mode == 0 ? p.Co : p.Ci;
+    for (int c = 0; c < p.BN; c += 16) {
+      uint32_t r[16];
+      tmem_ld_32x16(taddr + c, r);
+      tmem_ld_wait();
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        v[j] = __uint_as_float(r[j]);
+        if (p.bias) v[j] += __bfloat162float(p.bias[n0 + c + j]);
+        if (p.relu) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (p.pool) {
+        uint32_t packed[8];
+        uint32_t am[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float v01 = __shfl_xor_sync(0xffffffffu, v[j], 1);
+          const float v10 = __shfl_xor_sync(0xffffffffu, v[j], 16);
+          const float v11 = __shfl_xor_sync(0xffffffffu, v[j], 17);
+          float best = v[j];
+          uint32_t bi = 0;
+          if (v01 > best) { best = v01; bi = 1; }
+          if (v10 > best) { best = v10; bi = 2; }
+          if (v11 > best) { best = v11; bi = 3; }
+          const uint32_t hb = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(best));
+          if (j & 1) packed[j >> 1] |= hb << 16; else packed[j >> 1] = hb;
+          am[j >> 2] |= bi << (8 * (j & 3));
+        }
+        if (lane < 16 && !(lane & 1) && ww < p.W && h < p.H) {
+          const size_t o = (((size_t)img * (p.H / 2) + h / 2) * (p.W / 2) + ww / 2) * Cout + n0 + c;
+          *reinterpret_cast<uint4*>(p.out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+          *reinterpret_cast<uint4*>(p.out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+          if (p.argmax) *reinterpret_cast<uint4*>(p.argmax + o) = make_uint4(am[0], am[1], am[2], am[3]);
+        }
+      } else if (ww < p.W && h < p.H) {
+        const size_t o = (((size_t)img * p.H + h) * p.W + ww) * Cout + n0 + c;
+        uint2 lo = pack_bf16x4(make_float4(v[0], v[1], v[2], v[3])), l2 = pack_bf16x4(make_float4(v[4], v[5], v[6], v[7]));
+        uint2 hi = pack_bf16x4(make_float4(v[8], v[9], v[10], v[11])), h2 = pack_bf16x4(make_float4(v[12], v[13], v[14], v[15]));
+        *reinterpret_cast<uint4*>(p.out + o) = make_uint4(lo.x, lo.y, l2.x, l2.y);
+        *reinterpret_cast<uint4*>(p.out + o + 8) = make_uint4(hi.x, hi.y, h2.x, h2.y);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// wgrad: M tile = G stacked (tap, channel-block) pairs, G*CB = 128; K = pixels.
+// ------------------------------------------------------------------------------------------------
+struct WgradParams {
+  int B, H, W, Ci, Co, k, pad;
+  int CB;            // channels per A box: 32 (64-byte rows) or 64 (128-byte rows)
+  int G;             // pairs per M tile = 128 / CB
+  int cblocks;       // Ci / CB
+  int npairs;        // k*k*cblocks
+  int BN;
+  int tiles_h, ntiles, tiles_per_split;
+  float* dw;
+  uint32_t tmem_cols;
+  int nstage;
+};
+
+__global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn,
+                                                               const __grid_constant__ CUtensorMap tmDy, const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int box_bytes = TILE_PIX * p.CB * 2;          // one (tap, channel-block) box
+  const int a_bytes = p.G * box_bytes;                // 32 KB
+  const int b_bytes = p.BN * TILE_PIX * 2;
+  const int stage_bytes = a_bytes + b_bytes;
+  uint64_t* full = (uint64_t*)(smem + p.nstage * stage_bytes);
+  uint64_t* empty = full + p.nstage;
+  uint64_t* tmem_full = empty + p.nstage;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mt = blockIdx.x, n0 = blockIdx.y * p.BN;
+  const int t0 = blockIdx.z * p.tiles_per_split, t1 = min(p.ntiles, t0 + p.tiles_per_split);
+  if (t0 >= t1) return;
+  const int pair0 = mt * p.G;
+  const int npair_here = min(p.G, p.npairs - pair0);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmIn);
+    tma_prefetch_desc(&tmDy);
+    for (int s = 0; s < p.nstage; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t0; t < t1; ++t) {
+        const int img = t / p.tiles_h, h0 = (t % p.tiles_h) * TILE_H;
+        mbar_wait(empty + stage, phase ^ 1, 21);
+        uint8_t* sA = smem + stage * stage_bytes;
+        uint8_t* sB = sA + a_bytes;
+        mbar_arrive_expect_tx(full + stage, (uint32_t)(npair_here * box_bytes + b_bytes));
+        for (int j = 0; j < npair_here; ++j) {
+          const int pr = pair0 + j;
+          const int tap = pr / p.cblocks, cb = pr % p.cblocks;
+          const int kh = tap / p.k, kw = tap % p.k;
+          tma_load_4d(sA + j * box_bytes, &tmIn, full + stage, cb * p.CB, kw - p.pad, h0 + kh - p.pad, img);
+        }
+        for (int j = 0; j < p.BN / 64; ++j) tma_load_4d(sB + j * (TILE_PIX * 128), &tmDy, full + stage, n0 + 64 * j, 0, h0, img);
+        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.BN, 1, 1);
+      const uint32_t a_swz = p.CB == 64 ? SW_128B : SW_64B;
+      const int a_row = p.CB * 2;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t0; t < t1; ++t) {
+        mbar_wait(full + stage, phase, 22);
+        tc_fence_after();
+        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
+        const uint32_t sB = sA + a_bytes;
+        for (int ks = 0; ks < TILE_PIX / 16; ++ks) {
+          // 16 pixels (K) per instruction = two 8-row swizzle atoms
+          const uint64_t ad = make_smem_desc(sA + ks * 16 * a_row, box_bytes, 8 * a_row, a_swz);
+          const uint64_t bd = make_smem_desc(sB + ks * 2048, TILE_PIX * 128, 1024, SW_128B);
+          umma_bf16(tmem_base, ad, bd, idesc, (t > t0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit(empty + stage);
+        if (t == t1 - 1) umma_commit(tmem_full);
+        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    mbar_wait(tmem_full, 0, 23);
+    tc_fence_after();
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int j = row / p.CB, ch = row % p.CB;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const bool valid = j < npair_here;
+    const int pr = pair0 + (valid ? j : 0);
+    const int tap = pr / p.cblocks, cb = pr % p.cblocks;
+    float* dst_row = p.dw + ((size_t)tap * p.Ci + cb * p.CB + ch) * p.Co + n0;
+    for (int c = 0; c < p.BN; c += 16) {
+      uint32_t r[16];
+      tmem_ld_32x16(taddr + c, r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int e = 0; e < 16; e += 4)
+          red_add_f4(dst_row + c + e, make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]), __uint_as_float(r[e + 2]),
+                                                  __uint_as_float(r[e + 3])));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+// dbias[c] += sum over rows of dy[rows, C]
+__global__ void colsum_bf16_kernel(const bf16* __restrict__ dy, float* __restrict__ dbias, long long rows, int C) {
+  const long long per = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r0 = blockIdx.x * per, r1 = min(rows, r0 + per);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (long long r = r0; r < r1; ++r) s += __bfloat162float(dy[r * C + c]);
+    atomicAdd(dbias + c, s);
+  }
+}
+
+int act_tmap(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_c) {
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+  const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+  const uint32_t box[4] = {(uint32_t)box_c, TILE_W, TILE_H, 1};
+  return tc::make_tmap_bf16(tm, base, 4, dims, str, box, box_c * 2);
+}
+
+int set_smem(const void* fn) {
+  B200_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  return B200_OK;
+}
+
+int launch_conv(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W,
+                int Ci, int Co, int k, int relu, int pool, cudaStream_t st) {
+  const int Cred = mode == 0 ? Ci : Co;      // reduction channels
+  const int Cout = mode == 0 ? Co : Ci;      // channels produced
+  B200_REQUIRE(W <= TILE_W && W >= 1 && H >= 1, "conv_tc: W=%d must be <= 16", W);
+  B200_REQUIRE(k % 2 == 1 && k <= 7, "conv_tc: odd kernel size <= 7 expected, got %d", k);
+  B200_REQUIRE(Cred % 32 == 0, "conv_tc: reduction channels %d must be a multiple of 32", Cred);
+  B200_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "conv_tc: pooling needs even H, W");
+  ConvParams p;
+  p.B = B; p.H = H; p.W = W; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = k / 2; p.mode = mode;
+  p.KC = Cred % 64 == 0 ? 64 : 32;
+  p.kc_blocks = Cred / p.KC;
+  if (mode == 0) {
+    B200_REQUIRE(Cout % 64 == 0, "conv_tc fwd: output channels %d must be a multiple of 64", Cout);
+    p.BN = Cout % 128 == 0 ? 128 : 64;
+  } else {
+    B200_REQUIRE(Cout % 32 == 0, "conv_tc dgrad: input channels %d must be a multiple of 32", Cout);
+    p.BN = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
+  }
+  p.relu = relu; p.pool = pool; p.bias = (const bf16*)bias; p.out = (bf16*)out; p.argmax = argmax;
+  p.tiles_h = (H + TILE_H - 1) / TILE_H;
+  uint32_t cols = 32;
+  while ((int)cols < p.BN) cols <<= 1;
+  p.tmem_cols = cols;
+  const int a_bytes = TILE_PIX * p.KC * 2, b_bytes = p.BN * p.KC * 2;
+  const int stage_bytes = a_bytes + ((b_bytes + 1023) & ~1023);
+  p.nstage = 6;
+  while (p.nstage > 2 && (size_t)p.nstage * stage_bytes > 190 * 1024) --p.nstage;
+  const size_t smem = (size_t)p.nstage * stage_bytes + 1024 + 256;
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if ((rc = act_tmap(&tmA, act, B, H, W, Cred, p.KC))) return rc;
+  {
+    const uint64_t dims[2] = {(uint64_t)Co, (uint64_t)k * k * Ci}, str[1] = {(uint64_t)Co * 2};
+    if (mode == 0) {
+      const uint32_t box[2] = {64, (uint32_t)p.KC};
+      if ((rc = tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, 128))) return rc;
+    } else {
+      const uint32_t box[2] = {(uint32_t)p.KC, (uint32_t)p.BN};
+      if ((rc = tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, p.KC * 2))) return rc;
+    }
+  }
+  static bool attr = false;
+  if (!attr) { if ((rc = set_smem((const void*)conv_tc_kernel))) return rc; attr = true; }
+  dim3 grid(Cout / p.BN, B * p.tiles_h);
+  conv_tc_kernel<<<grid, 192, smem, st>>>(tmA, tmB, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_conv_tc_fwd(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W, int Ci,
+                     int Co, int k, int relu, int pool, void* stream) {
+  return launch_conv(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
+}
+
+int b200_conv_tc_dgrad(const void* dout, const void* w, void* din, const void* mask_src, int B, int H, int W, int Ci, int Co,
+                       int k, void* stream) {
+  (void)mask_src;
+  return launch_conv(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
+}
+
+int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co, int k,
+                       void* stream) {
+  B200_REQUIRE(W <= TILE_W, "conv_tc wgrad: W=%d must be <= 16", W);
+  B200_REQUIRE(Ci % 32 == 0 && (Ci == 32 || Ci % 64 == 0), "conv_tc wgrad: Ci=%d must be 32 or a multiple of 64", Ci);
+  B200_REQUIRE(Co % 64 == 0, "conv_tc wgrad: Co=%d must be a multiple of 64", Co);
+  cudaStream_t st = (cudaStream_t)stream;
+  WgradParams p;
+  p.B = B; p.H = H; p.W = W; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = k / 2;
+  p.CB = Ci == 32 ? 32 : 64;
+  p.G = 128 / p.CB;
+  p.cblocks = Ci / p.CB;
+  p.npairs = k * k * p.cblocks;
+  p.BN = Co % 128 == 0 ? 128 : 64;
+  p.tiles_h = (H + TILE_H - 1) / TILE_H;
+  p.ntiles = B * p.tiles_h;
+  p.dw = dw;
+  uint32_t cols = 32;
+  while ((int)cols < p.BN) cols <<= 1;
+  p.tmem_cols = cols;
+  const int mtiles = (p.npairs + p.G - 1) / p.G, ntile_n = Co / p.BN;
+  int split = (148 * 2) / (mtiles * ntile_n);
+  if (split < 1) split = 1;
+  if (split > p.ntiles) split = p.ntiles;
+  p.tiles_per_split = (p.ntiles + split - 1) / split;
+  split = (p.ntiles + p.tiles_per_split - 1) / p.tiles_per_split;
+  const int stage_bytes = 128 * 128 * 2 + p.BN * TILE_PIX * 2;
+  p.nstage = 4;
+  while (p.nstage > 2 && (size_t)p.nstage * stage_bytes > 190 * 1024) --p.nstage;
+  const size_t smem = (size_t)p.nstage * stage_bytes + 1024 + 256;
+  CUtensorMap tmIn, tmDy;
+  int rc;
+  if ((rc = act_tmap(&tmIn, in, B, H, W, Ci, p.CB))) return rc;
+  if ((rc = act_tmap(&tmDy, dout, B, H, W, Co, 64))) return rc;
+  static bool attr = false;
+  if (!attr) { if ((rc = set_smem((const void*)conv_wgrad_tc_kernel))) return rc; attr = true; }
+  conv_wgrad_tc_kernel<<<dim3(mtiles, ntile_n, split), 192, smem, st>>>(tmIn, tmDy, p);
+  B200_LAUNCH_CHECK();
+  if (dbias) {
+    colsum_bf16_kernel<<<148, Co < 256 ? (Co + 31) / 32 * 32 : 256, 0, st>>>((const bf16*)dout, dbias, (long long)B * H * W, Co);
+    B200_LAUNCH_CHECK();
+  }
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,256 @@
+// tcgen05 GEMM for sm_100a: D[M,N] = A.B, bf16 operands staged by TMA into 128B-swizzled shared
+// memory, fp32 accumulators in TMEM, warp-specialised (TMA producer / single-thread MMA issuer /
+// 4 epilogue warps), mbarrier pipeline, optional split-K with vector red.add.
+//
+// Replaces the cuBLAS/Eigen matmuls behind layers.dense (horovod/tensorflow_mnist.py:65-70;
+// horovod/tensorflow_mnist_gpu.py:62-66) — forward, dgrad and wgrad all map onto this kernel
+// through the K-major / MN-major operand switches, so weights and activations are never transposed
+// in memory.
+#include <mutex>
+
+#include "../include/b200dp.h"
+#include "tc_sm100.cuh"
+
+namespace tc {
+
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  });
+  return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box, uint32_t swizzle_bytes) {
+  EncodeTiledFn enc = get_encode_tiled();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  B200_REQUIRE(((uintptr_t)base & 15) == 0, "TMA base pointer %p is not 16-byte aligned", base);
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) {
+    B200_REQUIRE(strides_bytes[i] % 16 == 0, "TMA stride %llu of dim %d is not a multiple of 16 bytes", (unsigned long long)strides_bytes[i], i + 1);
+    gstr[i] = strides_bytes[i];
+  }
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu x %llu, box %u x %u)", (int)r,
+               rank, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 1), box[0], rank > 1 ? box[1] : 1);
+  return B200_OK;
+}
+
+}  // namespace tc
+
+namespace {
+
+using namespace tc;
+
+constexpr int BM = 128, BK = 64, NSTAGE = 4;
+constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
+
+struct GemmParams {
+  void* C;
+  int M, N, K, ldc;
+  int a_mn, b_mn, out_mode, bn;
+  int kb_total, kb_per_split;
+  uint32_t tmem_cols;
+};
+
+__global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = A_TILE_BYTES + p.bn * BK * 2;
+  uint64_t* full = (uint64_t*)(smem + NSTAGE * stage_bytes);
+  uint64_t* empty = full + NSTAGE;
+  uint64_t* tmem_full = empty + NSTAGE;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * p.bn, m0 = blockIdx.y * BM;
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+  if (kb0 >= kb1) return;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < NSTAGE; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty + stage, phase ^ 1, 1);
+        uint8_t* sA = smem + stage * stage_bytes;
+        uint8_t* sB = sA + A_TILE_BYTES;
+        mbar_arrive_expect_tx(full + stage, (uint32_t)stage_bytes);
+        const int k0 = kb * BK;
+        if (!p.a_mn) {
+          tma_load_2d(sA, &tmA, full + stage, k0, m0);
+        } else {
+          tma_load_2d(sA, &tmA, full + stage, m0, k0);
+          tma_load_2d(sA + 8192, &tmA, full + stage, m0 + 64, k0);
+        }
+        if (!p.b_mn) {
+          tma_load_2d(sB, &tmB, full + stage, k0, n0);
+        } else {
+          for (int j = 0; j < p.bn / 64; ++j) tma_load_2d(sB + j * 8192, &tmB, full + stage, n0 + 64 * j, k0);
+        }
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread drives the tensor core =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(BM, p.bn, p.a_mn, p.b_mn);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full + stage, phase, 2);
+        tc_fence_after();
+        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
+        const uint32_t sB = sA + A_TILE_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t ad = p.a_mn ? make_smem_desc(sA + k * 2048, 8192, 1024, SW_128B)
+                                     : make_smem_desc(sA + k * 32, 16, 1024, SW_128B);
+          const uint64_t bd = p.b_mn ? make_smem_desc(sB + k * 2048, 8192, 1024, SW_128B)
+                                     : make_smem_desc(sB + k * 32, 16, 1024, SW_128B);
+          umma_bf16(tmem_base, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(empty + stage);                 // frees the smem slot when these MMAs retire
+        if (kb == kb1 - 1) umma_commit(tmem_full);  // accumulator complete
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> global =====
+    mbar_wait(tmem_full, 0, 3);
+    tc_fence_after();
+    const int q = warp & 3;                         // TMEM lane quarter this warp may touch
+    const int row = m0 + q * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int c = 0; c < p.bn; c += 16) {
+      uint32_t r[16];
+      tmem_ld_32x16(taddr + c, r);
+      tmem_ld_wait();
+      if (row < p.M) {
+        const int col = n0 + c;
+        if (p.out_mode == 1) {
+          bf16* dst = (bf16*)p.C + (size_t)row * p.ldc + col;
+          if (col + 16 <= p.N) {
+            uint4 lo, hi;
+            uint2 t;
+            t = pack_bf16x4(make_float4(__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])));
+            lo.x = t.x; lo.y = t.y;
+            t = pack_bf16x4(make_float4(__uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7])));
+            lo.z = t.x; lo.w = t.y;
+            t = pack_bf16x4(make_float4(__uint_as_float(r[8]), __uint_as_float(r[9]), __uint_as_float(r[10]), __uint_as_float(r[11])));
+            hi.x = t.x; hi.y = t.y;
+            t = pack_bf16x4(make_float4(__uint_as_float(r[12]), __uint_as_float(r[13]), __uint_as_float(r[14]), __uint_as_float(r[15])));
+            hi.z = t.x; hi.w = t.y;
+            *reinterpret_cast<uint4*>(dst) = lo;
+            *reinterpret_cast<uint4*>(dst + 8) = hi;
+          } else {
+            for (int j = 0; j < 16 && col + j < p.N; ++j) dst[j] = __float2bfloat16(__uint_as_float(r[j]));
+          }
+        } else {
+          float* dst = (float*)p.C + (size_t)row * p.ldc + col;
+          if (col + 16 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+              const float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+              if (p.out_mode == 2) red_add_f4(dst + j, v);
+              else st_f4(dst + j, v);
+            }
+          } else {
+            for (int j = 0; j < 16 && col + j < p.N; ++j) {
+              if (p.out_mode == 2) atomicAdd(dst + j, __uint_as_float(r[j]));
+              else dst[j] = __uint_as_float(r[j]);
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+}  // namespace
+
+extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                            int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream) {
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: bad shape %dx%dx%d", M, N, K);
+  B200_REQUIRE(out_mode >= 0 && out_mode <= 2, "gemm_tc: out_mode %d", out_mode);
+  B200_REQUIRE(split_k >= 1, "gemm_tc: split_k %d", split_k);
+  B200_REQUIRE(split_k == 1 || out_mode == 2, "gemm_tc: split_k > 1 needs out_mode 2 (atomic accumulate)");
+  B200_REQUIRE(block_n >= 16 && block_n <= 256 && block_n % 16 == 0, "gemm_tc: block_n %d must be a multiple of 16 in [16,256]", block_n);
+  B200_REQUIRE(!b_mn_major || block_n % 64 == 0, "gemm_tc: MN-major B needs block_n %% 64 == 0 (got %d)", block_n);
+  B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tc: lda/ldb must be multiples of 8 elements (16 bytes)");
+  B200_REQUIRE(ldc % 4 == 0 && ((uintptr_t)C & 15) == 0, "gemm_tc: C must be 16-byte aligned with ldc %% 4 == 0");
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a_mn_major) {   // stored [M,K]
+    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)lda * 2};
+    const uint32_t box[2] = {64, 128};
+    if ((rc = tc::make_tmap_bf16(&tmA, A, 2, dims, str, box, 128))) return rc;
+  } else {             // stored [K,M]
+    const uint64_t dims[2] = {(uint64_t)M, (uint64_t)K}, str[1] = {(uint64_t)lda * 2};
+    const uint32_t box[2] = {64, 64};
+    if ((rc = tc::make_tmap_bf16(&tmA, A, 2, dims, str, box, 128))) return rc;
+  }
+  if (!b_mn_major) {   // stored [N,K]
+    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)ldb * 2};
+    const uint32_t box[2] = {64, (uint32_t)block_n};
+    if ((rc = tc::make_tmap_bf16(&tmB, B, 2, dims, str, box, 128))) return rc;
+  } else {             // stored [K,N]
+    const uint64_t dims[2] = {(uint64_t)N, (uint64_t)K}, str[1] = {(uint64_t)ldb * 2};
+    const uint32_t box[2] = {64, 64};
+    if ((rc = tc::make_tmap_bf16(&tmB, B, 2, dims, str, box, 128))) return rc;
+  }
+  GemmParams p;
+  p.C = C; p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.a_mn = a_mn_major; p.b_mn = b_mn_major; p.out_mode = out_mode; p.bn = block_n;
+  p.kb_total = (K + BK - 1) / BK;
+  if (split_k > p.kb_total) split_k = p.kb_total;
+  p.kb_per_split = (p.kb_total + split_k - 1) / split_k;
+  split_k = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  uint32_t cols = 32;
+  while ((int)cols < block_n) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t smem = (size_t)NSTAGE * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    B200_CHECK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    smem_set = 200 * 1024;
+  }
+  B200_REQUIRE(smem <= 200 * 1024, "gemm_tc: %zu bytes of shared memory needed", smem);
+  dim3 grid((N + block_n - 1) / block_n, (M + BM - 1) / BM, split_k);
+  gemm_tc_kernel<<<grid, 192, smem, (cudaStream_t)stream>>>(tmA, tmB, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -1,0 +1,619 @@
+// CUDA-core kernels: the thin first convolution (K=25, too thin for tensor cores), the fused
+// classifier head, pooling backward, and direct/tiled fallbacks used for unusual shapes and as the
+// on-device oracle of the tcgen05 kernels.  Replaces the TensorFlow kernels the reference calls at
+// horovod/tensorflow_mnist.py:42-73 and horovod/tensorflow_mnist_gpu.py:47-88.
+#include "../include/b200dp.h"
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float bf(const bf16* p) { return __bfloat162float(*p); }
+
+// ------------------------------------------------------------------------------------------------
+// conv1: 5x5 SAME, Cin=1 -> C1, + bias + ReLU + 2x2 maxpool, one image per block.
+// Lane = output channel (weights live in registers), input tile + halo in shared memory.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __restrict__ x, const bf16* __restrict__ w,
+                                                             const bf16* __restrict__ bias, bf16* __restrict__ out,
+                                                             uint8_t* __restrict__ argmax, int C1, int* step_ptr,
+                                                             int bump_step, float* loss_ring, int* correct_ring, int ring) {
+  __shared__ float img[32][33];
+  const int b = blockIdx.x;
+  if (bump_step && b == 0 && threadIdx.x == 0 && step_ptr) {
+    const int s = *step_ptr + 1;          // the step that starts now
+    *step_ptr = s;
+    if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+  }
+  for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) {
+    const int r = i >> 5, c = i & 31;
+    const int yy = r - 2, xx = c - 2;
+    img[r][c] = (yy >= 0 && yy < 28 && xx >= 0 && xx < 28) ? x[(size_t)b * 784 + yy * 28 + xx] : 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + lane;
+    float wr[25];
+#pragma unroll
+    for (int t = 0; t < 25; ++t) wr[t] = c < C1 ? bf(w + t * C1 + c) : 0.f;
+    const float bb = c < C1 ? bf(bias + c) : 0.f;
+    for (int p = warp; p < 196; p += nwarp) {
+      const int ph = p / 14, pw = p % 14;
+      float best = -1.f;
+      int bi = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int y = 2 * ph + (q >> 1), xq = 2 * pw + (q & 1);
+        float acc = bb;
+#pragma unroll
+        for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) acc = fmaf(img[y + kh][xq + kw], wr[kh * 5 + kw], acc);
+        acc = fmaxf(acc, 0.f);
+        if (acc > best) { best = acc; bi = q; }
+      }
+      if (c < C1) {
+        const size_t o = ((size_t)b * 196 + p) * C1 + c;
+        out[o] = __float2bfloat16(best);
+        argmax[o] = (uint8_t)bi;
+      }
+    }
+  }
+}
+
+// conv1 weight gradient straight from the pooled-activation gradient: the pooling window passes the
+// gradient to its argmax position only, so
+//   dW[tap,c] = sum_{b,ph,pw} x[b, 2ph+i*+kh-2, 2pw+j*+kw-2] * da1[b,ph,pw,c] * (a1 > 0).
+__global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x, const bf16* __restrict__ da1,
+                                                          const bf16* __restrict__ a1, const uint8_t* __restrict__ argmax,
+                                                          float* __restrict__ dw, float* __restrict__ dbias, int B, int C1) {
+  __shared__ float img[32][33];
+  __shared__ float red[8][26][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + lane;
+    float acc[26];
+#pragma unroll
+    for (int t = 0; t < 26; ++t) acc[t] = 0.f;
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) {
+        const int r = i >> 5, cc = i & 31;
+        const int yy = r - 2, xx = cc - 2;
+        img[r][cc] = (yy >= 0 && yy < 28 && xx >= 0 && xx < 28) ? x[(size_t)b * 784 + yy * 28 + xx] : 0.f;
+      }
+      __syncthreads();
+      if (c < C1) {
+        for (int p = warp; p < 196; p += nwarp) {
+          const size_t o = ((size_t)b * 196 + p) * C1 + c;
+          const float g = bf(a1 + o) > 0.f ? bf(da1 + o) : 0.f;
+          const int q = argmax[o];
+          const int y = 2 * (p / 14) + (q >> 1), xq = 2 * (p % 14) + (q & 1);
+#pragma unroll
+          for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(img[y + kh][xq + kw], g, acc[kh * 5 + kw]);
+          acc[25] += g;
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < 26; ++t) red[warp][t][lane] = acc[t];
+    __syncthreads();
+    for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
+      const int t = i >> 5, l = i & 31;
+      float s = 0.f;
+      for (int wv = 0; wv < nwarp; ++wv) s += red[wv][t][l];
+      if (c0 + l < C1) {
+        if (t < 25) atomicAdd(dw + t * C1 + c0 + l, s);
+        else atomicAdd(dbias + c0 + l, s);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Classifier head, one batch row per block:
+//   h = dropout(relu(z + b1));  logits = h W2 + b2;  loss/acc;  dlogits = (softmax - onehot)/B;
+//   dz = (dlogits W2^T) * relu'/dropout mask.   z is cleared afterwards (split-K accumulator).
+// ------------------------------------------------------------------------------------------------
+template <int NC_MAX>
+__global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z, const bf16* __restrict__ b1,
+                                                           const bf16* __restrict__ w2, const bf16* __restrict__ b2,
+                                                           const int* __restrict__ labels, bf16* __restrict__ h_out,
+                                                           bf16* __restrict__ dz_out, float* __restrict__ dlogits_out,
+                                                           float* __restrict__ logits_out, float* __restrict__ loss_sum,
+                                                           int* __restrict__ correct, int B, int D, int NC, float drop_rate,
+                                                           int training, uint64_t seed, const int* step_ptr, int layer_id,
+                                                           int zero_z, int ring) {
+  extern __shared__ float hs[];            // D floats: bf16-rounded h
+  __shared__ float part[8][NC_MAX];
+  __shared__ float dl[NC_MAX];
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const bool drop = training && drop_rate > 0.f;
+  const uint32_t step = step_ptr ? (uint32_t)*step_ptr : 0u;
+  const uint32_t thresh = (uint32_t)fminf(drop_rate * 4294967296.f, 4294967295.f);
+  const float keep_scale = drop ? 1.f / (1.f - drop_rate) : 1.f;
+  float acc[NC_MAX];
+#pragma unroll
+  for (int k = 0; k < NC_MAX; ++k) acc[k] = 0.f;
+  float* zr = z + (size_t)b * D;
+  for (int j4 = tid * 4; j4 < D; j4 += blockDim.x * 4) {
+    float4 zv = *reinterpret_cast<float4*>(zr + j4);
+    if (zero_z) *reinterpret_cast<float4*>(zr + j4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 rnd = make_uint4(~0u, ~0u, ~0u, ~0u);
+    if (drop) rnd = dropout_rand4((uint32_t)(((size_t)b * D + j4) >> 2), step, (uint32_t)layer_id, seed);
+    const float zz[4] = {zv.x, zv.y, zv.z, zv.w};
+    const uint32_t rr[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int j = j4 + e;
+      float hv = fmaxf(zz[e] + bf(b1 + j), 0.f);
+      hv = (!drop || rr[e] >= thresh) ? hv * keep_scale : 0.f;
+      const bf16 hb = __float2bfloat16(hv);
+      h_out[(size_t)b * D + j] = hb;
+      hv = __bfloat162float(hb);
+      hs[j] = hv;
+      if (hv != 0.f) {
+#pragma unroll
+        for (int k = 0; k < NC_MAX; ++k)
+          if (k < NC) acc[k] = fmaf(hv, bf(w2 + (size_t)j * NC + k), acc[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NC_MAX; ++k) {
+    const float s = warp_sum(acc[k]);
+    if (lane == 0) part[warp][k] = s;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float lg[NC_MAX], mx = -1e30f;
+    int am = 0;
+    for (int k = 0; k < NC; ++k) {
+      float s = bf(b2 + k);
+      for (int wv = 0; wv < nwarp; ++wv) s += part[wv][k];
+      lg[k] = s;
+      if (logits_out) logits_out[(size_t)b * NC + k] = s;
+      if (s > mx) { mx = s; am = k; }
+    }
+    float se = 0.f;
+    for (int k = 0; k < NC; ++k) se += expf(lg[k] - mx);
+    const int y = labels[b];
+    const float lse = mx + logf(se);
+    const float invB = 1.f / (float)B;
+    const int slot = ring > 0 ? (int)(step % (uint32_t)ring) : 0;   // ring > 0: per-step mean loss, else running sum
+    atomicAdd(loss_sum + slot, ring > 0 ? (lse - lg[y]) * invB : lse - lg[y]);
+    if (am == y) atomicAdd(correct + slot, 1);
+    for (int k = 0; k < NC; ++k) {
+      const float d = (expf(lg[k] - lse) - (k == y ? 1.f : 0.f)) * invB;
+      dl[k] = d;
+      if (dlogits_out) dlogits_out[(size_t)b * NC + k] = d;
+    }
+  }
+  if (!training || dz_out == nullptr) return;
+  __syncthreads();
+  float dlr[NC_MAX];
+#pragma unroll
+  for (int k = 0; k < NC_MAX; ++k) dlr[k] = k < NC ? dl[k] : 0.f;
+  for (int j = tid; j < D; j += blockDim.x) {
+    float g = 0.f;
+    if (hs[j] > 0.f) {
+#pragma unroll
+      for (int k = 0; k < NC_MAX; ++k)
+        if (k < NC) g = fmaf(dlr[k], bf(w2 + (size_t)j * NC + k), g);
+      g *= keep_scale;
+    }
+    dz_out[(size_t)b * D + j] = __float2bfloat16(g);
+  }
+}
+
+// dW2[j,k] = sum_b h[b,j] dlogits[b,k];  db1[j] = sum_b dz[b,j];  db2[k] = sum_b dlogits[b,k]
+template <int NC_MAX>
+__global__ void __launch_bounds__(128) head_wgrad_kernel(const bf16* __restrict__ h, const bf16* __restrict__ dz,
+                                                         const float* __restrict__ dlogits, float* __restrict__ dw2,
+                                                         float* __restrict__ db2, float* __restrict__ db1, int B, int D, int NC) {
+  __shared__ float red[16][8][NC_MAX + 1];
+  const int jj = threadIdx.x & 7, bl = threadIdx.x >> 3;       // 8 columns x 16 batch lanes
+  const int j = blockIdx.x * 8 + jj;
+  float acc[NC_MAX + 1];
+#pragma unroll
+  for (int k = 0; k <= NC_MAX; ++k) acc[k] = 0.f;
+  if (j < D) {
+    for (int b = bl; b < B; b += 16) {
+      const float hv = bf(h + (size_t)b * D + j);
+      acc[NC_MAX] += bf(dz + (size_t)b * D + j);
+      if (hv != 0.f) {
+#pragma unroll
+        for (int k = 0; k < NC_MAX; ++k)
+          if (k < NC) acc[k] = fmaf(hv, dlogits[(size_t)b * NC + k], acc[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k <= NC_MAX; ++k) red[bl][jj][k] = acc[k];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 8 * (NC_MAX + 1); i += blockDim.x) {
+    const int c = i / (NC_MAX + 1), k = i % (NC_MAX + 1);
+    const int col = blockIdx.x * 8 + c;
+    if (col >= D) continue;
+    float s = 0.f;
+    for (int r = 0; r < 16; ++r) s += red[r][c][k];
+    if (k == NC_MAX) db1[col] = s;
+    else if (k < NC) dw2[(size_t)col * NC + k] = s;
+  }
+  if (blockIdx.x == 0 && (int)threadIdx.x < NC) {
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dlogits[(size_t)b * NC + threadIdx.x];
+    db2[threadIdx.x] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void unpool_relu_bwd_kernel(const bf16* __restrict__ dpool, const bf16* __restrict__ pooled,
+                                       const uint8_t* __restrict__ argmax, bf16* __restrict__ dy, int HP, int WP, int C,
+                                       long long total) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long p = i / C;
+    const int pw = (int)(p % WP); p /= WP;
+    const int ph = (int)(p % HP);
+    const long long b = p / HP;
+    const float g = bf(pooled + i) > 0.f ? bf(dpool + i) : 0.f;
+    const int q = argmax[i];
+    const int W = 2 * WP;
+    const size_t base = (((size_t)b * 2 * HP + 2 * ph) * W + 2 * pw) * C + c;
+    const bf16 zero = __float2bfloat16(0.f), gv = __float2bfloat16(g);
+    dy[base] = q == 0 ? gv : zero;
+    dy[base + C] = q == 1 ? gv : zero;
+    dy[base + (size_t)W * C] = q == 2 ? gv : zero;
+    dy[base + (size_t)W * C + C] = q == 3 ? gv : zero;
+  }
+}
+
+__global__ void maxpool_fwd_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, uint8_t* __restrict__ argmax,
+                                   int H, int W, int C, long long total) {
+  const int HP = H / 2, WP = W / 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long p = i / C;
+    const int pw = (int)(p % WP); p /= WP;
+    const int ph = (int)(p % HP);
+    const long long b = p / HP;
+    const size_t base = (((size_t)b * H + 2 * ph) * W + 2 * pw) * C + c;
+    const float v0 = bf(in + base), v1 = bf(in + base + C), v2 = bf(in + base + (size_t)W * C), v3 = bf(in + base + (size_t)W * C + C);
+    float best = v0; int q = 0;
+    if (v1 > best) { best = v1; q = 1; }
+    if (v2 > best) { best = v2; q = 2; }
+    if (v3 > best) { best = v3; q = 3; }
+    out[i] = __float2bfloat16(best);
+    if (argmax) argmax[i] = (uint8_t)q;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Direct convolutions (fallback / oracle).  Output spatial size Ho = H + 2*pad - k + 1.
+// ------------------------------------------------------------------------------------------------
+__global__ void conv_direct_fwd_kernel(const bf16* __restrict__ in, const bf16* __restrict__ w, const bf16* __restrict__ bias,
+                                       bf16* __restrict__ out, int H, int W, int Ci, int Co, int k, int pad, int relu,
+                                       long long total) {
+  const int Ho = H + 2 * pad - k + 1, Wo = W + 2 * pad - k + 1;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int co = (int)(i % Co);
+    long long p = i / Co;
+    const int wo = (int)(p % Wo); p /= Wo;
+    const int ho = (int)(p % Ho);
+    const long long b = p / Ho;
+    float acc = bias ? bf(bias + co) : 0.f;
+    for (int kh = 0; kh < k; ++kh) {
+      const int hi = ho + kh - pad;
+      if (hi < 0 || hi >= H) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int wi = wo + kw - pad;
+        if (wi < 0 || wi >= W) continue;
+        const bf16* ip = in + (((size_t)b * H + hi) * W + wi) * Ci;
+        const bf16* wp = w + ((size_t)(kh * k + kw) * Ci) * Co + co;
+        for (int ci = 0; ci < Ci; ++ci) acc = fmaf(bf(ip + ci), bf(wp + (size_t)ci * Co), acc);
+      }
+    }
+    if (relu) acc = fmaxf(acc, 0.f);
+    out[i] = __float2bfloat16(acc);
+  }
+}
+
+__global__ void conv_direct_dgrad_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ w, bf16* __restrict__ din,
+                                         int H, int W, int Ci, int Co, int k, int pad, long long total) {
+  const int Ho = H + 2 * pad - k + 1, Wo = W + 2 * pad - k + 1;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % Ci);
+    long long p = i / Ci;
+    const int wi = (int)(p % W); p /= W;
+    const int hi = (int)(p % H);
+    const long long b = p / H;
+    float acc = 0.f;
+    for (int kh = 0; kh < k; ++kh) {
+      const int ho = hi - kh + pad;
+      if (ho < 0 || ho >= Ho) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int wo = wi - kw + pad;
+        if (wo < 0 || wo >= Wo) continue;
+        const bf16* dp = dout + (((size_t)b * Ho + ho) * Wo + wo) * Co;
+        const bf16* wp = w + ((size_t)(kh * k + kw) * Ci + ci) * Co;
+        for (int co = 0; co < Co; ++co) acc = fmaf(bf(dp + co), bf(wp + co), acc);
+      }
+    }
+    din[i] = __float2bfloat16(acc);
+  }
+}
+
+// one thread per (tap, ci, co); blockIdx.y splits the batch; fp32 atomics into dw / dbias
+__global__ void conv_direct_wgrad_kernel(const bf16* __restrict__ in, const bf16* __restrict__ dout, float* __restrict__ dw,
+                                         float* __restrict__ dbias, int B, int H, int W, int Ci, int Co, int k, int pad) {
+  const int Ho = H + 2 * pad - k + 1, Wo = W + 2 * pad - k + 1;
+  const long long total = (long long)k * k * Ci * Co;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int co = (int)(i % Co);
+  long long p = i / Co;
+  const int ci = (int)(p % Ci); p /= Ci;
+  const int kw = (int)(p % k), kh = (int)(p / k);
+  const int bchunk = (B + gridDim.y - 1) / gridDim.y;
+  const int b0 = blockIdx.y * bchunk, b1 = min(B, b0 + bchunk);
+  float acc = 0.f, bacc = 0.f;
+  const bool do_bias = dbias != nullptr && kh == 0 && kw == 0 && ci == 0;
+  for (int b = b0; b < b1; ++b)
+    for (int ho = 0; ho < Ho; ++ho) {
+      const int hi = ho + kh - pad;
+      const bool hin = hi >= 0 && hi < H;
+      if (!hin && !do_bias) continue;
+      for (int wo = 0; wo < Wo; ++wo) {
+        const float d = bf(dout + (((size_t)b * Ho + ho) * Wo + wo) * Co + co);
+        if (do_bias) bacc += d;
+        const int wi = wo + kw - pad;
+        if (hin && wi >= 0 && wi < W) acc = fmaf(bf(in + (((size_t)b * H + hi) * W + wi) * Ci + ci), d, acc);
+      }
+    }
+  atomicAdd(dw + i, acc);
+  if (do_bias) atomicAdd(dbias + co, bacc);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tiled CUDA-core GEMM, 64x64 tile, 16-deep k slices, 4x4 register micro-tile.
+// ------------------------------------------------------------------------------------------------
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256) gemm_simple_kernel(const bf16* __restrict__ A, const bf16* __restrict__ Bm, void* __restrict__ C,
+                                                          int M, int N, int K, int accumulate, int out_bf16) {
+  __shared__ float As[16][65], Bs[16][65];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+      int mm, kk;
+      if (TA) { mm = i & 63; kk = i >> 6; } else { kk = i & 15; mm = i >> 4; }
+      const int gm = m0 + mm, gk = k0 + kk;
+      float v = 0.f;
+      if (gm < M && gk < K) v = bf(TA ? A + (size_t)gk * M + gm : A + (size_t)gm * K + gk);
+      As[kk][mm] = v;
+    }
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+      int nn, kk;
+      if (TB) { kk = i & 15; nn = i >> 4; } else { nn = i & 63; kk = i >> 6; }
+      const int gn = n0 + nn, gk = k0 + kk;
+      float v = 0.f;
+      if (gn < N && gk < K) v = bf(TB ? Bm + (size_t)gn * K + gk : Bm + (size_t)gk * N + gn);
+      Bs[kk][nn] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[kk][ty * 4 + i]; b[i] = Bs[kk][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      const int gm = m0 + ty * 4 + i, gn = n0 + tx * 4 + j;
+      if (gm >= M || gn >= N) continue;
+      const size_t o = (size_t)gm * N + gn;
+      if (out_bf16) {
+        bf16* c = (bf16*)C;
+        c[o] = __float2bfloat16(acc[i][j] + (accumulate ? __bfloat162float(c[o]) : 0.f));
+      } else {
+        float* c = (float*)C;
+        c[o] = acc[i][j] + (accumulate ? c[o] : 0.f);
+      }
+    }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ s, bf16* __restrict__ d, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    d[i] = __float2bfloat16(s[i]);
+}
+
+__global__ void bias_relu_bf16_kernel(const float* __restrict__ z, const bf16* __restrict__ bias, bf16* __restrict__ out,
+                                      int cols, int relu, long long total) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    float v = z[i] + (bias ? bf(bias + (i % cols)) : 0.f);
+    if (relu) v = fmaxf(v, 0.f);
+    out[i] = __float2bfloat16(v);
+  }
+}
+
+__global__ void adam_local_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
+                                  bf16* __restrict__ w16, long long n, float b1, float b2, float eps, float step_size,
+                                  float vscale, float gscale) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gg = g[i] * gscale;
+    const float mm = b1 * m[i] + (1.f - b1) * gg;
+    const float vv = b2 * v[i] + (1.f - b2) * gg * gg;
+    const float pp = p[i] - step_size * mm / (sqrtf(vv) * vscale + eps);
+    m[i] = mm; v[i] = vv; p[i] = pp;
+    if (w16) w16[i] = __float2bfloat16(pp);
+  }
+}
+
+__global__ void l2_flush_kernel(float4* p, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = make_float4(1.f, 2.f, 3.f, (float)i);
+}
+
+inline int grid_for(long long total, int threads, int cap = 148 * 16) {
+  long long g = (total + threads - 1) / threads;
+  if (g < 1) g = 1;
+  return (int)(g > cap ? cap : g);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_conv1_pool_fwd(const float* x, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int C1,
+                        int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream) {
+  B200_REQUIRE(B > 0 && C1 > 0, "conv1: bad shape B=%d C1=%d", B, C1);
+  conv1_pool_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)w, (const bf16*)bias, (bf16*)out, argmax, C1,
+                                                            step_ptr, bump_step, loss_ring, correct_ring, ring);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_conv1_wgrad(const float* x, const void* da1, const void* a1, const uint8_t* argmax, float* dw, float* dbias,
+                     int B, int C1, void* stream) {
+  B200_REQUIRE(B > 0 && C1 > 0, "conv1 wgrad: bad shape");
+  const int grid = B < 148 ? B : 148;
+  conv1_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)da1, (const bf16*)a1, argmax, dw, dbias, B, C1);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, const int* labels, void* h, void* dz,
+                      float* dlogits, float* logits_out, float* loss_sum, int* correct, int B, int D, int NC,
+                      float drop_rate, int training, uint64_t seed, const int* step_ptr, int layer_id, int zero_z,
+                      int ring, void* stream) {
+  B200_REQUIRE(NC >= 1 && NC <= 16, "head: NC=%d outside [1,16]", NC);
+  B200_REQUIRE(D % 4 == 0 && D > 0 && (size_t)D * 4 <= 200 * 1024, "head: D=%d must be a multiple of 4 and fit shared memory", D);
+  B200_REQUIRE(drop_rate >= 0.f && drop_rate < 1.f, "head: drop_rate %f", drop_rate);
+  const size_t smem = (size_t)D * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CHECK(cudaFuncSetAttribute(head_fwd_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  head_fwd_bwd_kernel<16><<<B, 256, smem, (cudaStream_t)stream>>>(z, (const bf16*)b1, (const bf16*)w2, (const bf16*)b2, labels,
+                                                                 (bf16*)h, (bf16*)dz, dlogits, logits_out, loss_sum, correct, B,
+                                                                 D, NC, drop_rate, training, seed, step_ptr, layer_id, zero_z, ring);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* dw2, float* db2, float* db1, int B, int D,
+                    int NC, void* stream) {
+  B200_REQUIRE(NC >= 1 && NC <= 16, "head wgrad: NC=%d outside [1,16]", NC);
+  head_wgrad_kernel<16><<<cdiv(D, 8), 128, 0, (cudaStream_t)stream>>>((const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, int B, int HP, int WP,
+                         int C, void* stream) {
+  const long long total = (long long)B * HP * WP * C;
+  unpool_relu_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)dpool, (const bf16*)pooled, argmax,
+                                                                                 (bf16*)dy, HP, WP, C, total);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_maxpool_fwd(const void* in, void* out, uint8_t* argmax, int B, int H, int W, int C, void* stream) {
+  B200_REQUIRE(H % 2 == 0 && W % 2 == 0, "maxpool: odd spatial size %dx%d", H, W);
+  const long long total = (long long)B * (H / 2) * (W / 2) * C;
+  maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)in, (bf16*)out, argmax, H, W, C, total);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_conv_direct_fwd(const void* in, const void* w, const void* bias, void* out, int B, int H, int W, int Ci, int Co,
+                         int k, int pad, int relu, void* stream) {
+  const int Ho = H + 2 * pad - k + 1, Wo = W + 2 * pad - k + 1;
+  B200_REQUIRE(Ho > 0 && Wo > 0, "conv: empty output");
+  const long long total = (long long)B * Ho * Wo * Co;
+  conv_direct_fwd_kernel<<<grid_for(total, 256, 1 << 20), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)in, (const bf16*)w, (const bf16*)bias, (bf16*)out, H, W, Ci, Co, k, pad, relu, total);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_conv_direct_dgrad(const void* dout, const void* w, void* din, int B, int H, int W, int Ci, int Co, int k, int pad,
+                           void* stream) {
+  const long long total = (long long)B * H * W * Ci;
+  conv_direct_dgrad_kernel<<<grid_for(total, 256, 1 << 20), 256, 0, (cudaStream_t)stream>>>((const bf16*)dout, (const bf16*)w,
+                                                                                           (bf16*)din, H, W, Ci, Co, k, pad, total);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_conv_direct_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co,
+                           int k, int pad, void* stream) {
+  const long long total = (long long)k * k * Ci * Co;
+  const int gx = cdiv(total, 128);
+  int gy = (148 * 8 + gx - 1) / gx;
+  if (gy > B) gy = B;
+  if (gy < 1) gy = 1;
+  conv_direct_wgrad_kernel<<<dim3(gx, gy), 128, 0, (cudaStream_t)stream>>>((const bf16*)in, (const bf16*)dout, dw, dbias, B, H, W,
+                                                                          Ci, Co, k, pad);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_gemm_simple(const void* A, const void* Bm, void* C, int M, int N, int K, int transA, int transB, int accumulate,
+                     int out_bf16, void* stream) {
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape %dx%dx%d", M, N, K);
+  dim3 grid(cdiv(N, 64), cdiv(M, 64));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!transA && !transB) gemm_simple_kernel<false, false><<<grid, 256, 0, st>>>((const bf16*)A, (const bf16*)Bm, C, M, N, K, accumulate, out_bf16);
+  if (transA && !transB) gemm_simple_kernel<true, false><<<grid, 256, 0, st>>>((const bf16*)A, (const bf16*)Bm, C, M, N, K, accumulate, out_bf16);
+  if (!transA && transB) gemm_simple_kernel<false, true><<<grid, 256, 0, st>>>((const bf16*)A, (const bf16*)Bm, C, M, N, K, accumulate, out_bf16);
+  if (transA && transB) gemm_simple_kernel<true, true><<<grid, 256, 0, st>>>((const bf16*)A, (const bf16*)Bm, C, M, N, K, accumulate, out_bf16);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
+  cast_f32_bf16_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(src, (bf16*)dst, n);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_bias_relu_bf16(const float* z, const void* bias, void* out, int rows, int cols, int relu, void* stream) {
+  const long long total = (long long)rows * cols;
+  bias_relu_bf16_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(z, (const bf16*)bias, (bf16*)out, cols, relu, total);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_adam_local(float* master, float* m, float* v, const float* grad, void* w16, long long n, int step, double lr,
+                    double b1, double b2, double eps, int eps_mode, float grad_scale, void* stream) {
+  B200_REQUIRE(step >= 1, "adam: step must be >= 1");
+  const double bc1 = 1.0 - pow(b1, (double)step), bc2 = 1.0 - pow(b2, (double)step);
+  const float step_size = (float)(eps_mode == 0 ? lr * sqrt(bc2) / bc1 : lr / bc1);
+  const float vscale = (float)(eps_mode == 0 ? 1.0 : 1.0 / sqrt(bc2));
+  adam_local_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(master, m, v, grad, (bf16*)w16, n, (float)b1, (float)b2,
+                                                                        (float)eps, step_size, vscale, grad_scale);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_l2_flush(void* scratch, size_t bytes, void* stream) {
+  l2_flush_kernel<<<148 * 4, 512, 0, (cudaStream_t)stream>>>((float4*)scratch, bytes / 16);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // extern "C"

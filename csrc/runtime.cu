@@ -1,0 +1,54 @@
+// Host-side runtime helpers: topology discovery (what Open MPI/Horovod learn at MPI_Init,
+// horovod/tensorflow_mnist.py:90) — GPUs, SM counts, memory, and the peer-access (NVLink/NVSwitch) matrix.
+#include <string>
+
+#include "../include/b200dp.h"
+#include "common.cuh"
+
+extern "C" int b200_topology_json(char* buf, int buflen) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) n = 0;
+  std::string s = "{\"gpus\":[";
+  for (int d = 0; d < n; ++d) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, d) != cudaSuccess) continue;
+    char pci[32];
+    snprintf(pci, sizeof pci, "%04x:%02x:%02x.0", p.pciDomainID, p.pciBusID, p.pciDeviceID);
+    char tmp[512];
+    snprintf(tmp, sizeof tmp,
+             "%s{\"index\":%d,\"name\":\"%s\",\"cc\":\"%d.%d\",\"sms\":%d,\"mem_bytes\":%zu,\"l2_bytes\":%d,"
+             "\"smem_per_block_optin\":%zu,\"pci\":\"%s\"}",
+             d ? "," : "", d, p.name, p.major, p.minor, p.multiProcessorCount, p.totalGlobalMem, p.l2CacheSize,
+             p.sharedMemPerBlockOptin, pci);
+    s += tmp;
+  }
+  s += "],\"peer_access\":[";
+  for (int a = 0; a < n; ++a) {
+    s += a ? ",[" : "[";
+    for (int b = 0; b < n; ++b) {
+      int can = a == b;
+      if (a != b) cudaDeviceCanAccessPeer(&can, a, b);
+      s += (b ? "," : "");
+      s += can ? "1" : "0";
+    }
+    s += "]";
+  }
+  s += "],\"p2p_native_atomics\":[";
+  for (int a = 0; a < n; ++a) {
+    s += a ? ",[" : "[";
+    for (int b = 0; b < n; ++b) {
+      int v = a == b;
+      if (a != b) cudaDeviceGetP2PAttribute(&v, cudaDevP2PAttrNativeAtomicSupported, a, b);
+      s += (b ? "," : "");
+      s += v ? "1" : "0";
+    }
+    s += "]";
+  }
+  s += "]}";
+  if ((int)s.size() + 1 > buflen) {
+    b200_set_error("topology buffer too small: need %zu", s.size() + 1);
+    return -(int)(s.size() + 1);
+  }
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return (int)s.size();
+}

@@ -1,0 +1,122 @@
+/* libb200dp — C ABI of the sm_100a kernels and the peer-memory collective runtime.
+ *
+ * Every function returns 0 on success; on failure b200_last_error() describes why.
+ * Pointers are device pointers unless stated; `stream` is a cudaStream_t passed as void*.
+ * Activations are NHWC bf16, weights use TensorFlow layouts (conv HWIO, dense [in,out]).
+ * Reference citations (path:line) are relative to the upstream repository.
+ */
+#ifndef B200DP_H
+#define B200DP_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_MAX_RANKS 8
+#define B200_MAX_CHANNELS 16
+#define B200_MAX_COMM_BLOCKS 64
+#define B200_MAX_RANGES 4
+#define B200_MAX_SEGMENTS 32
+
+typedef void* b200_comm_t;
+
+const char* b200_last_error(void);
+
+/* ---- collective runtime (replaces Horovod core + MPI/NCCL ops; horovod/Dockerfile:64-65) ---- */
+size_t b200_comm_pad_bytes(void);
+int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out);
+int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
+int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out /* 64 B or NULL */);
+int b200_comm_seg_open(b200_comm_t h, int seg_id, const void* all_handles /* nranks x 64 B */);
+void* b200_comm_seg_ptr(b200_comm_t h, int seg_id, int peer);
+int b200_comm_destroy(b200_comm_t h);
+
+/* DistributedOptimizer's hot path (horovod/tensorflow_mnist.py:133-136): gradient allreduce fused with the
+ * 1/size scale, the Adam update (horovod/tensorflow_mnist.py:130) and the bf16 weight refresh. */
+int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthreads, int reduce,
+                              int grad_seg, size_t grad_cur_off, size_t grad_other_off,
+                              int state_seg, size_t master_off, size_t m_off, size_t v_off,
+                              int w16_seg, size_t w16_off, int ctrl_seg, size_t step_off, size_t hyper_off,
+                              float scale, int nranges, const long long* range_start, const long long* range_numel,
+                              const int* range_algo, const int* range_zero_other, void* stream);
+/* hvd.allreduce (Average/Sum) on a staged fp32 buffer */
+int b200_allreduce(b200_comm_t h, int channel, int nblocks, int nthreads, int algo, int src_seg, size_t src_off,
+                   int dst_seg, size_t dst_off, long long numel, float scale, void* stream);
+/* hvd.broadcast / BroadcastGlobalVariablesHook (horovod/tensorflow_mnist.py:143) */
+int b200_broadcast(b200_comm_t h, int channel, int nblocks, int nthreads, int root, int src_seg, size_t src_off,
+                   int dst_seg, size_t dst_off, long long numel, void* stream);
+int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads, int seg, size_t off, long long numel,
+                          void* stream);
+/* hvd.Adasum (horovod/tensorflow_mnist.py:133), one tree level per call */
+size_t b200_adasum_scratch_bytes(int nblocks, int nseg);
+int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cur_seg, size_t cur_off, int next_seg,
+                      size_t next_off, int scratch_seg, size_t scratch_off, int nseg, const long long* seg_start,
+                      const long long* seg_numel, void* stream);
+
+/* ---- model kernels, CUDA-core family (first conv, head, fallbacks) ---- */
+/* conv 5x5 SAME Cin=1 + bias + ReLU + maxpool2 (horovod/tensorflow_mnist.py:49-53). step_ptr (may be NULL)
+ * is incremented by one when bump_step != 0: the step counter Adam and dropout read; with ring > 0 the
+ * new step's slot of the loss/correct rings is cleared at the same time. */
+int b200_conv1_pool_fwd(const float* x, const void* w_bf16, const void* bias_bf16, void* out_bf16, uint8_t* argmax,
+                        int B, int C1, int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring,
+                        void* stream);
+int b200_conv1_wgrad(const float* x, const void* da1_bf16, const void* a1_bf16, const uint8_t* argmax,
+                     float* dw, float* dbias, int B, int C1, void* stream);
+/* dense1 epilogue + dropout + logits + softmax-xent fwd/bwd + accuracy (horovod/tensorflow_mnist.py:65-73).
+ * ring == 0: loss_sum/correct are running sums; ring > 0: they are rings indexed by *step_ptr % ring and
+ * receive the batch-mean loss / correct count of that step. */
+int b200_head_fwd_bwd(float* z, const void* b1_bf16, const void* w2_bf16, const void* b2_bf16, const int* labels,
+                      void* h_bf16, void* dz_bf16, float* dlogits, float* logits_out, float* loss_sum, int* correct,
+                      int B, int D, int NC, float drop_rate, int training, uint64_t seed, const int* step_ptr,
+                      int layer_id, int zero_z, int ring, void* stream);
+int b200_head_wgrad(const void* h_bf16, const void* dz_bf16, const float* dlogits, float* dw2, float* db2, float* db1,
+                    int B, int D, int NC, void* stream);
+/* max-pool 2x2/2 backward fused with the ReLU mask: dy[b,2h+i,2w+j,c] */
+int b200_unpool_relu_bwd(const void* dpool_bf16, const void* pooled_bf16, const uint8_t* argmax, void* dy_bf16,
+                         int B, int HP, int WP, int C, void* stream);
+int b200_maxpool_fwd(const void* in_bf16, void* out_bf16, uint8_t* argmax, int B, int H, int W, int C, void* stream);
+/* direct convolution fallbacks (any k, stride 1), NHWC bf16, fp32 accumulate */
+int b200_conv_direct_fwd(const void* in, const void* w, const void* bias, void* out, int B, int H, int W, int Ci,
+                         int Co, int k, int pad, int relu, void* stream);
+int b200_conv_direct_dgrad(const void* dout, const void* w, void* din, int B, int H, int W, int Ci, int Co, int k,
+                           int pad, void* stream);
+int b200_conv_direct_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci,
+                           int Co, int k, int pad, void* stream);
+/* C[M,N] (+)= op(A) op(B); bf16 in, fp32 accumulate; CUDA-core fallback and on-device oracle.
+ * transA: A is [K,M]; transB: B is [N,K]. out_bf16: C stored as bf16 (else fp32). */
+int b200_gemm_simple(const void* A, const void* B, void* C, int M, int N, int K, int transA, int transB,
+                     int accumulate, int out_bf16, void* stream);
+int b200_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+int b200_adam_local(float* master, float* m, float* v, const float* grad, void* w16, long long n, int step, double lr,
+                    double b1, double b2, double eps, int eps_mode, float grad_scale, void* stream);
+int b200_bias_relu_bf16(const float* z, const void* bias_bf16, void* out_bf16, int rows, int cols, int relu, void* stream);
+
+/* ---- model kernels, tcgen05 family (UMMA + TMEM + TMA) ---- */
+/* D[M,N] = A.B with bf16 operands, fp32 accumulation in TMEM.
+ *   a_mn_major=0: A stored [M,K] (K contiguous);  =1: A stored [K,M] (M contiguous)
+ *   b_mn_major=0: B stored [N,K] (K contiguous);  =1: B stored [K,N] (N contiguous)
+ *   out_mode 0: fp32 store, 1: bf16 store, 2: fp32 atomic accumulate (required when split_k > 1)
+ *   lda/ldb/ldc are row pitches in elements of the stored matrices. */
+int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                 int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream);
+/* Implicit-GEMM 5x5/3x3 SAME convolution on tensor cores, taps applied by shifted TMA boxes (no im2col buffer).
+ *   mode 0 forward: out = relu(conv(in, w) + bias), optionally followed by maxpool2 (+argmax)
+ *   mode 1 dgrad  : din = conv_transpose(dout, w)  */
+int b200_conv_tc_fwd(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W,
+                     int Ci, int Co, int k, int relu, int pool, void* stream);
+int b200_conv_tc_dgrad(const void* dout, const void* w, void* din, const void* mask_src, int B, int H, int W, int Ci,
+                       int Co, int k, void* stream);
+int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co,
+                       int k, void* stream);
+
+/* ---- host runtime ---- */
+/* JSON description of the visible GPUs: names, SM counts, memory, peer-access matrix. Returns bytes written. */
+int b200_topology_json(char* buf, int buflen);
+int b200_l2_flush(void* scratch, size_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,177 @@
+"""Peer-memory collectives with all ranks emulated on ONE GPU (blockIdx.y = rank, cooperative launch).
+Covers the flag/epoch protocol across repeated steps, one-shot and two-shot reductions, the fused
+Adam epilogue (bitwise equal on every rank), broadcast, all-gather and Adasum (SURVEY §4.3 'Collective')."""
+import ctypes
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from b200dp.models.torch_ref import adam_step_
+from b200dp.ops import kernels as K
+from b200dp.parallel.arena import SymmetricArena
+from b200dp.parallel.collectives import adasum_tree
+
+bf16 = torch.bfloat16
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Rig:
+    def __init__(self, n, numel):
+        self.n, self.numel = n, numel
+        self.a = SymmetricArena.emulated(n)
+        self.a.set_timeout_ms(2000)
+        self.ctrl = self.a.alloc(256)
+        self.state = self.a.alloc(numel * 4 * 3)
+        self.grad = self.a.alloc(numel * 4 * 2)
+        self.w16 = self.a.alloc(numel * 2)
+        for r in range(n):
+            self.a.view(self.ctrl, 16, 5, torch.float64, r).copy_(torch.tensor([1e-3, 0.9, 0.999, 1e-8, 0.0], dtype=torch.float64))
+
+    def t(self, seg, off_elems, dtype, r, es=4):
+        return self.a.view(seg, off_elems * es, self.numel, dtype, r)
+
+    def set_step(self, s):
+        for r in range(self.n):
+            self.a.view(self.ctrl, 0, 1, torch.int32, r).fill_(s)
+
+    def fused(self, parity, ranges, reduce=True, scale=None, nblocks=8):
+        N = self.numel
+        self.a.fused_allreduce_adam(channel=1, nblocks=nblocks, nthreads=256, reduce=reduce, grad_seg=self.grad,
+                                    grad_cur_off=parity * N * 4, grad_other_off=(1 - parity) * N * 4, state_seg=self.state,
+                                    master_off=0, m_off=N * 4, v_off=2 * N * 4, w16_seg=self.w16, w16_off=0, ctrl_seg=self.ctrl,
+                                    step_off=0, hyper_off=16, scale=(1.0 / self.n if scale is None else scale), ranges=ranges)
+
+    def close(self):
+        self.a.close()
+
+
+@pytest.mark.parametrize("n", [1, 2, 4, 8])
+@pytest.mark.parametrize("algo", [0, 1])
+def test_fused_allreduce_adam_steps(n, algo):
+    torch.manual_seed(n * 10 + algo)
+    N = 4096 * 3 + 64
+    rig = Rig(n, N)
+    try:
+        master0 = torch.randn(N, device="cuda")
+        for r in range(n):
+            rig.t(rig.state, 0, torch.float32, r).copy_(master0)
+        pr, mr, vr = master0.clone(), torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        ranges = [(0, 4096, algo, 1), (4096, N - 4096, 1 - algo if n > 1 else 0, 1)]
+        for step in range(1, 6):
+            par = step & 1
+            rig.set_step(step)
+            grads = [torch.randn(N, device="cuda") for _ in range(n)]
+            for r in range(n):
+                rig.t(rig.grad, par * N, torch.float32, r).copy_(grads[r])
+                rig.t(rig.grad, (1 - par) * N, torch.float32, r).fill_(7.0)      # stale: must come back zeroed
+            rig.fused(par, ranges)
+            torch.cuda.synchronize()
+            g = grads[0].clone()
+            for r in range(1, n):
+                g += grads[r]
+            g *= 1.0 / n
+            adam_step_(pr, g, mr, vr, step, lr=1e-3)
+            w0 = rig.t(rig.w16, 0, bf16, 0, es=2)
+            for r in range(n):
+                # bf16 working weights: complete and bitwise identical on every rank
+                assert torch.equal(rig.t(rig.w16, 0, bf16, r, es=2), w0), f"step {step}: rank {r} weights differ from rank 0"
+                assert torch.count_nonzero(rig.t(rig.grad, (1 - par) * N, torch.float32, r)).item() == 0
+            assert torch.allclose(w0.float(), pr.to(bf16).float(), rtol=1e-2, atol=1e-3)
+            # fp32 master: one-shot ranges are replicated; two-shot ranges live on their owner
+            for (st, ln, al, _) in ranges:
+                for r in range(n):
+                    mine = rig.t(rig.state, 0, torch.float32, r)[st:st + ln]
+                    if al == 0 or n == 1:
+                        assert torch.allclose(mine, pr[st:st + ln], rtol=1e-5, atol=1e-6)
+                    else:
+                        chunk = (math.ceil(ln / n) + 3) // 4 * 4
+                        lo, hi = min(r * chunk, ln), min((r + 1) * chunk, ln)
+                        assert torch.allclose(mine[lo:hi], pr[st + lo:st + hi], rtol=1e-5, atol=1e-6)
+        # gather the sharded master back (checkpoint path) and compare everything
+        if n > 1:
+            for (st, ln, al, _) in ranges:
+                if al == 1:
+                    rig.a.allgather_slices_(rig.state, st * 4, ln)
+            torch.cuda.synchronize()
+            for r in range(n):
+                assert torch.allclose(rig.t(rig.state, 0, torch.float32, r), pr, rtol=1e-5, atol=1e-6)
+    finally:
+        rig.close()
+
+
+def test_fused_local_only_path_after_adasum():
+    rig = Rig(4, 1024)
+    try:
+        for r in range(4):
+            rig.t(rig.state, 0, torch.float32, r).fill_(1.0)
+            rig.t(rig.grad, 0, torch.float32, r).fill_(float(r + 1))
+        rig.set_step(1)
+        rig.fused(0, [(0, 1024, 1, 0)], reduce=False, scale=1.0)
+        torch.cuda.synchronize()
+        vals = [rig.t(rig.state, 0, torch.float32, r)[0].item() for r in range(4)]
+        assert all(abs(v - (1.0 - 1e-3)) < 1e-6 for v in vals)       # first Adam step moves by lr regardless of |g|
+    finally:
+        rig.close()
+
+
+@pytest.mark.parametrize("n", [2, 8])
+@pytest.mark.parametrize("algo", [0, 1])
+def test_plain_allreduce_broadcast(n, algo):
+    torch.manual_seed(n)
+    N = 10_000
+    a = SymmetricArena.emulated(n)
+    a.set_timeout_ms(2000)
+    try:
+        seg = a.alloc(N * 4 * 2)
+        xs = [torch.randn(N, device="cuda") for _ in range(n)]
+        for it in range(3):
+            for r in range(n):
+                a.view(seg, 0, N, torch.float32, r).copy_(xs[r] * (it + 1))
+            K.check(K.lib().b200_allreduce(a.h, 2, 4, 256, algo, seg, 0, seg, N * 4, N, 1.0 / n, _stream()))
+            torch.cuda.synchronize()
+            want = sum(xs) * (it + 1) / n
+            first = a.view(seg, N * 4, N, torch.float32, 0)
+            for r in range(n):
+                got = a.view(seg, N * 4, N, torch.float32, r)
+                assert torch.allclose(got, want, rtol=1e-5, atol=1e-5)
+                assert torch.equal(got, first)
+        root = n - 1
+        K.check(K.lib().b200_broadcast(a.h, 3, 4, 256, root, seg, 0, seg, N * 4, N, _stream()))
+        torch.cuda.synchronize()
+        for r in range(n):
+            assert torch.equal(a.view(seg, N * 4, N, torch.float32, r), xs[root] * 3)
+    finally:
+        a.close()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_adasum_levels_match_tree(n):
+    torch.manual_seed(n + 100)
+    sizes = [800, 32, 5000, 64, 10]
+    N = sum(sizes)
+    N4 = (N + 3) // 4 * 4
+    a = SymmetricArena.emulated(n)
+    a.set_timeout_ms(2000)
+    try:
+        E = N4 * 4
+        seg = a.alloc(E * 2 + 65536)
+        xs = [torch.randn(N, device="cuda") * (r + 1) for r in range(n)]
+        for r in range(n):
+            a.view(seg, 0, N, torch.float32, r).copy_(xs[r])
+        starts = [sum(sizes[:i]) for i in range(len(sizes))]
+        res = a.adasum_levels(seg, 0, E, 2 * E, starts, sizes, nblocks=8)
+        torch.cuda.synchronize()
+        want = torch.cat([adasum_tree([x[s:s + l].cpu() for x in xs]) for s, l in zip(starts, sizes)])
+        first = a.view(seg, res, N, torch.float32, 0)
+        for r in range(n):
+            got = a.view(seg, res, N, torch.float32, r)
+            assert torch.equal(got, first), f"rank {r} differs bitwise from rank 0"
+            assert torch.allclose(got.cpu(), want, rtol=1e-4, atol=1e-5)
+    finally:
+        a.close()
