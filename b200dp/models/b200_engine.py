@@ -67,7 +67,7 @@ def _env_flag(name: str, default: str = "1") -> bool:
 class B200Engine(Engine):
     def __init__(self, spec: Optional[ModelSpec] = None, optimizer=None, *, seed: int = 0, batch_size: int = 128,
                  use_graph: Optional[bool] = None, dropout: bool = True, use_tc: Optional[bool] = None,
-                 comm_blocks: int = 32, arena: Optional[SymmetricArena] = None, **_ignored):
+                 comm_blocks: int = 296, arena: Optional[SymmetricArena] = None, **_ignored):
         self.spec = spec or get_spec()
         if self.spec.arch != "mnist_cnn":
             raise NotImplementedError(f"B200Engine implements the mnist_cnn family; use engine='torch' for {self.spec.arch}")
@@ -147,6 +147,7 @@ class B200Engine(Engine):
                         for _ in range(3)]
         self._pin_i = 0
         self.comm_stream = torch.cuda.Stream(device=dev)
+        self.side_stream = torch.cuda.Stream(device=dev)
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._warm: set = set()
         self.dist: Optional[DistributedAdam] = None
@@ -228,47 +229,72 @@ class B200Engine(Engine):
                            drop_rate=0.0, training=False, seed=self.seed, step_ptr=None, zero_z=True, ring=0)
 
     def _backward_and_update(self, B: int, par: int) -> None:
+        """Backward as a small DAG over three streams (captured as graph branches):
+
+            main : dense dgrad -> unpool (+conv2 bias grad) -> conv2 dgrad -> conv1 wgrad -> comm(rest)
+            side1: head wgrad, dense wgrad                    -> comm(dense bucket), underneath the conv backward
+            side2: conv2 wgrad (needs dy2 only)
+        """
         w, g = self.w16, self.grads[par]
         main = torch.cuda.current_stream()
-        K.head_wgrad(self.h[:B], self.dz[:B], self.dlogits[:B], self.pv("out.kernel", g), self.pv("out.bias", g), self.pv("dense.bias", g))
+        s1, s2 = self.comm_stream, self.side_stream
         a2f = self.a2[:B].view(B, self.F)
         gd = self.pv("dense.kernel", g)
         wd = self.pv("dense.kernel", w)
         dpool = self.dpool[:B].view(B, self.F)
+        ev_head = torch.cuda.Event()
+        ev_head.record(main)
+        # ---- side 1: gradients that only need the head's outputs
+        s1.wait_event(ev_head)
+        with torch.cuda.stream(s1):
+            K.head_wgrad(self.h[:B], self.dz[:B], self.dlogits[:B], self.pv("out.kernel", g), self.pv("out.bias", g),
+                         self.pv("dense.bias", g))
+            if self.tc_dense:
+                K.gemm_tc(a2f, self.dz[:B], gd, self.F, self.D, B, a_mn_major=True, b_mn_major=True, out_mode=0, block_n=128)
+            else:
+                K.gemm_simple(a2f, self.dz[:B], gd, self.F, self.D, B, transA=True)
+        # ---- main: the dgrad chain
         if self.tc_dense:
-            K.gemm_tc(a2f, self.dz[:B], gd, self.F, self.D, B, a_mn_major=True, b_mn_major=True, out_mode=0, block_n=128)
             K.gemm_tc(self.dz[:B], wd, dpool, B, self.F, self.D, out_mode=1, block_n=32)
         else:
-            K.gemm_simple(a2f, self.dz[:B], gd, self.F, self.D, B, transA=True)
             K.gemm_simple(self.dz[:B], wd, dpool, B, self.F, self.D, transB=True)
-        # dense bucket: gradient complete and W no longer read -> reduce+update underneath the conv backward
-        ev = torch.cuda.Event()
-        ev.record(main)
+        ev_dgrad = torch.cuda.Event()
+        ev_dgrad.record(main)
         if not self.adasum:
-            self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
+            # dense bucket: gradient complete (side 1) and W no longer read (dgrad done)
+            s1.wait_event(ev_dgrad)
+            with torch.cuda.stream(s1):
                 self._comm(0, self.comm_dense, par)
-            ev_done = torch.cuda.Event()
-            ev_done.record(self.comm_stream)
-        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B])
+        ev_s1 = torch.cuda.Event()
+        ev_s1.record(s1)
+        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B], self.pv("conv2.bias", g))
+        ev_dy = torch.cuda.Event()
+        ev_dy.record(main)
         k2 = self.pv("conv2.kernel", w)
+        s2.wait_event(ev_dy)
+        with torch.cuda.stream(s2):
+            if self.tc_conv:
+                K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None)
+            else:
+                K.conv_direct_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, 2)
+            ev_s2 = torch.cuda.Event()
+            ev_s2.record(s2)
         if self.tc_conv:
-            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), self.pv("conv2.bias", g))
             K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B])
         else:
-            K.conv_direct_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), self.pv("conv2.bias", g), 2)
             K.conv_direct_dgrad(self.dy2[:B], k2, self.da1[:B], 2)
         K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        main.wait_event(ev_s2)
+        main.wait_event(ev_s1)
         if self.adasum:
             self._adasum_update(par)
         else:
             self._comm(1, self.comm_rest, par)
-            main.wait_event(ev_done)
 
     def _comm(self, channel: int, ranges, par: int, *, reduce: Optional[bool] = None, grad_off: Optional[int] = None,
               scale: Optional[float] = None) -> None:
         T4 = self.T * 4
-        nb = self.comm_blocks if sum(r[1] for r in ranges) >= (1 << 20) else 8
+        nb = self.comm_blocks if sum(r[1] for r in ranges) >= (1 << 20) else 16
         self.arena.fused_allreduce_adam(
             channel=channel, nblocks=nb, nthreads=512, reduce=self.reduce if reduce is None else reduce,
             grad_seg=self.seg_grad, grad_cur_off=par * T4 if grad_off is None else grad_off, grad_other_off=(1 - par) * T4,

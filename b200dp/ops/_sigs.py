@@ -30,7 +30,7 @@ _SIGS = {
     "b200_conv1_wgrad": (I, [P, P, P, P, P, P, I, I, P]),
     "b200_head_fwd_bwd": (I, [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, I, U64, P, I, I, I, P]),
     "b200_head_wgrad": (I, [P, P, P, P, P, P, I, I, I, P]),
-    "b200_unpool_relu_bwd": (I, [P, P, P, P, I, I, I, I, P]),
+    "b200_unpool_relu_bwd": (I, [P, P, P, P, P, I, I, I, I, P]),
     "b200_maxpool_fwd": (I, [P, P, P, I, I, I, I, P]),
     "b200_conv_direct_fwd": (I, [P, P, P, P, I, I, I, I, I, I, I, I, P]),
     "b200_conv_direct_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, P]),

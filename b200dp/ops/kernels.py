@@ -80,10 +80,10 @@ def head_wgrad(h, dz, dlogits, dw2, db2, db1):
                                 _p(dw2), _p(db2), _p(db1), B, D, NC, _stream()), "head_wgrad")
 
 
-def unpool_relu_bwd(dpool, pooled, argmax, dy):
+def unpool_relu_bwd(dpool, pooled, argmax, dy, dbias=None):
     B, HP, WP, Cc = pooled.shape
     check(lib().b200_unpool_relu_bwd(_p(_chk(dpool, bf16, "dpool")), _p(_chk(pooled, bf16, "pooled")), _p(argmax), _p(_chk(dy, bf16, "dy")),
-                                     B, HP, WP, Cc, _stream()), "unpool_relu_bwd")
+                                     _p(dbias), B, HP, WP, Cc, _stream()), "unpool_relu_bwd")
 
 
 def maxpool_fwd(inp, out, argmax):

@@ -117,17 +117,6 @@ __device__ __forceinline__ float adam_elem(float g, float& p, float& m, float& v
   return p;
 }
 
-__device__ __forceinline__ void adam_vec4(const FusedArgs& a, const AdamCoef& c, long long i, float4 g) {
-  float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
-  adam_elem(g.x, p.x, m.x, v.x, c);
-  adam_elem(g.y, p.y, m.y, v.y, c);
-  adam_elem(g.z, p.z, m.z, v.z, c);
-  adam_elem(g.w, p.w, m.w, v.w, c);
-  st_f4(a.master + i, p);
-  st_f4(a.m + i, m);
-  st_f4(a.v + i, v);
-}
-
 __device__ __forceinline__ float4 reduce_peers(const FusedArgs& a, long long i) {
   float4 s = ld_f4(a.grad[0] + i);
   if (a.reduce) {
@@ -174,16 +163,28 @@ __global__ void __launch_bounds__(512) fused_allreduce_adam_kernel(const FusedAr
   for (int ri = 0; ri < a.nranges; ++ri) {
     const Range rg = a.ranges[ri];
     if (rg.algo == 0 || !multi) {
-      // one-shot: every rank reduces and updates the whole range
-      for (long long q = tid; q < rg.numel / 4; q += nthr) {
-        const long long i = rg.start + q * 4;
-        const float4 g = reduce_peers(a, i);
-        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
-        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
-        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
-        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
-        *reinterpret_cast<uint2*>(a.w16[a.rank] + i) = pack_bf16x4(p);
-        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(0.f, 0.f, 0.f, 0.f));
+      // one-shot: every rank reduces and updates the whole range (two vectors in flight per thread)
+      const long long nq = rg.numel / 4;
+      for (long long q = tid; q < nq; q += 2 * nthr) {
+        const long long i0 = rg.start + q * 4;
+        const bool two = q + nthr < nq;
+        const long long i1 = two ? i0 + nthr * 4 : i0;
+        const float4 g0 = reduce_peers(a, i0);
+        const float4 g1 = two ? reduce_peers(a, i1) : g0;
+        float4 p0 = ld_f4(a.master + i0), m0 = ld_f4(a.m + i0), v0 = ld_f4(a.v + i0);
+        float4 p1 = ld_f4(a.master + i1), m1 = ld_f4(a.m + i1), v1 = ld_f4(a.v + i1);
+        adam_elem(g0.x, p0.x, m0.x, v0.x, c); adam_elem(g0.y, p0.y, m0.y, v0.y, c);
+        adam_elem(g0.z, p0.z, m0.z, v0.z, c); adam_elem(g0.w, p0.w, m0.w, v0.w, c);
+        st_f4(a.master + i0, p0); st_f4(a.m + i0, m0); st_f4(a.v + i0, v0);
+        *reinterpret_cast<uint2*>(a.w16[a.rank] + i0) = pack_bf16x4(p0);
+        if (rg.zero_other) st_f4(a.grad_other + i0, make_float4(0.f, 0.f, 0.f, 0.f));
+        if (two) {
+          adam_elem(g1.x, p1.x, m1.x, v1.x, c); adam_elem(g1.y, p1.y, m1.y, v1.y, c);
+          adam_elem(g1.z, p1.z, m1.z, v1.z, c); adam_elem(g1.w, p1.w, m1.w, v1.w, c);
+          st_f4(a.master + i1, p1); st_f4(a.m + i1, m1); st_f4(a.v + i1, v1);
+          *reinterpret_cast<uint2*>(a.w16[a.rank] + i1) = pack_bf16x4(p1);
+          if (rg.zero_other) st_f4(a.grad_other + i1, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
       }
     } else {
       // two-shot: reduce + update the owned slice, push the bf16 result to every rank

@@ -19,7 +19,7 @@ __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __rest
                                                              int bump_step, float* loss_ring, int* correct_ring, int ring) {
   __shared__ float img[32][33];
   const int b = blockIdx.x;
-  if (bump_step && b == 0 && threadIdx.x == 0 && step_ptr) {
+  if (bump_step && b == 0 && blockIdx.y == 0 && threadIdx.x == 0 && step_ptr) {
     const int s = *step_ptr + 1;          // the step that starts now
     *step_ptr = s;
     if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __rest
 #pragma unroll
     for (int t = 0; t < 25; ++t) wr[t] = c < C1 ? bf(w + t * C1 + c) : 0.f;
     const float bb = c < C1 ? bf(bias + c) : 0.f;
-    for (int p = warp; p < 196; p += nwarp) {
+    for (int p = blockIdx.y * 49 + warp; p < (blockIdx.y + 1) * 49; p += nwarp) {
       const int ph = p / 14, pw = p % 14;
       float best = -1.f;
       int bi = 0;
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
       }
       __syncthreads();
       if (c < C1) {
-        for (int p = warp; p < 196; p += nwarp) {
+        for (int p = blockIdx.y * 49 + warp; p < (blockIdx.y + 1) * 49; p += nwarp) {
           const size_t o = ((size_t)b * 196 + p) * C1 + c;
           const float g = bf(a1 + o) > 0.f ? bf(da1 + o) : 0.f;
           const int q = argmax[o];
@@ -212,24 +212,26 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
 
 // dW2[j,k] = sum_b h[b,j] dlogits[b,k];  db1[j] = sum_b dz[b,j];  db2[k] = sum_b dlogits[b,k]
 template <int NC_MAX>
-__global__ void __launch_bounds__(128) head_wgrad_kernel(const bf16* __restrict__ h, const bf16* __restrict__ dz,
+__global__ void __launch_bounds__(256) head_wgrad_kernel(const bf16* __restrict__ h, const bf16* __restrict__ dz,
                                                          const float* __restrict__ dlogits, float* __restrict__ dw2,
                                                          float* __restrict__ db2, float* __restrict__ db1, int B, int D, int NC) {
-  __shared__ float red[16][8][NC_MAX + 1];
-  const int jj = threadIdx.x & 7, bl = threadIdx.x >> 3;       // 8 columns x 16 batch lanes
+  __shared__ float red[32][8][NC_MAX + 1];
+  extern __shared__ float dls[];                                // B x NC dlogits, staged once per block
+  for (int i = threadIdx.x; i < B * NC; i += blockDim.x) dls[i] = dlogits[i];
+  __syncthreads();
+  const int jj = threadIdx.x & 7, bl = threadIdx.x >> 3;       // 8 columns x 32 batch lanes
   const int j = blockIdx.x * 8 + jj;
   float acc[NC_MAX + 1];
 #pragma unroll
   for (int k = 0; k <= NC_MAX; ++k) acc[k] = 0.f;
   if (j < D) {
-    for (int b = bl; b < B; b += 16) {
+#pragma unroll 4
+    for (int b = bl; b < B; b += 32) {
       const float hv = bf(h + (size_t)b * D + j);
       acc[NC_MAX] += bf(dz + (size_t)b * D + j);
-      if (hv != 0.f) {
 #pragma unroll
-        for (int k = 0; k < NC_MAX; ++k)
-          if (k < NC) acc[k] = fmaf(hv, dlogits[(size_t)b * NC + k], acc[k]);
-      }
+      for (int k = 0; k < NC_MAX; ++k)
+        if (k < NC) acc[k] = fmaf(hv, dls[b * NC + k], acc[k]);
     }
   }
 #pragma unroll
@@ -240,28 +242,34 @@ __global__ void __launch_bounds__(128) head_wgrad_kernel(const bf16* __restrict_
     const int col = blockIdx.x * 8 + c;
     if (col >= D) continue;
     float s = 0.f;
-    for (int r = 0; r < 16; ++r) s += red[r][c][k];
+    for (int r = 0; r < 32; ++r) s += red[r][c][k];
     if (k == NC_MAX) db1[col] = s;
     else if (k < NC) dw2[(size_t)col * NC + k] = s;
   }
   if (blockIdx.x == 0 && (int)threadIdx.x < NC) {
     float s = 0.f;
-    for (int b = 0; b < B; ++b) s += dlogits[(size_t)b * NC + threadIdx.x];
+    for (int b = 0; b < B; ++b) s += dls[b * NC + threadIdx.x];
     db2[threadIdx.x] = s;
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void unpool_relu_bwd_kernel(const bf16* __restrict__ dpool, const bf16* __restrict__ pooled,
-                                       const uint8_t* __restrict__ argmax, bf16* __restrict__ dy, int HP, int WP, int C,
-                                       long long total) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+// grid-stride with a stride that is a multiple of C: every thread stays on one channel, so the conv bias
+// gradient (sum of dy over batch and space) accumulates in a register and costs one atomic per thread group.
+__global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const bf16* __restrict__ dpool, const bf16* __restrict__ pooled,
+                                                              const uint8_t* __restrict__ argmax, bf16* __restrict__ dy,
+                                                              float* __restrict__ dbias, int HP, int WP, int C, long long total) {
+  __shared__ float red[256];
+  float bsum = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int c = (int)(i % C);
     long long p = i / C;
     const int pw = (int)(p % WP); p /= WP;
     const int ph = (int)(p % HP);
     const long long b = p / HP;
     const float g = bf(pooled + i) > 0.f ? bf(dpool + i) : 0.f;
+    bsum += g;
     const int q = argmax[i];
     const int W = 2 * WP;
     const size_t base = (((size_t)b * 2 * HP + 2 * ph) * W + 2 * pw) * C + c;
@@ -270,6 +278,20 @@ __global__ void unpool_relu_bwd_kernel(const bf16* __restrict__ dpool, const bf1
     dy[base + C] = q == 1 ? gv : zero;
     dy[base + (size_t)W * C] = q == 2 ? gv : zero;
     dy[base + (size_t)W * C + C] = q == 3 ? gv : zero;
+  }
+  if (dbias == nullptr) return;
+  // blockDim (256) and the stride are multiples of C when C divides 256; otherwise fall back to per-thread atomics
+  if (256 % C == 0) {
+    red[threadIdx.x] = bsum;
+    __syncthreads();
+    if ((int)threadIdx.x < C) {
+      float s = 0.f;
+      for (int t = threadIdx.x; t < 256; t += C) s += red[t];
+      atomicAdd(dbias + threadIdx.x, s);
+    }
+  } else if (stride % C == 0) {
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (first < total) atomicAdd(dbias + (int)(first % C), bsum);
   }
 }
 
@@ -479,7 +501,7 @@ extern "C" {
 int b200_conv1_pool_fwd(const float* x, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int C1,
                         int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1: bad shape B=%d C1=%d", B, C1);
-  conv1_pool_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)w, (const bf16*)bias, (bf16*)out, argmax, C1,
+  conv1_pool_fwd_kernel<<<dim3(B, 4), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)w, (const bf16*)bias, (bf16*)out, argmax, C1,
                                                             step_ptr, bump_step, loss_ring, correct_ring, ring);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -489,7 +511,7 @@ int b200_conv1_wgrad(const float* x, const void* da1, const void* a1, const uint
                      int B, int C1, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1 wgrad: bad shape");
   const int grid = B < 148 ? B : 148;
-  conv1_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)da1, (const bf16*)a1, argmax, dw, dbias, B, C1);
+  conv1_wgrad_kernel<<<dim3(grid, 4), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)da1, (const bf16*)a1, argmax, dw, dbias, B, C1);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -517,16 +539,23 @@ int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, 
 int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* dw2, float* db2, float* db1, int B, int D,
                     int NC, void* stream) {
   B200_REQUIRE(NC >= 1 && NC <= 16, "head wgrad: NC=%d outside [1,16]", NC);
-  head_wgrad_kernel<16><<<cdiv(D, 8), 128, 0, (cudaStream_t)stream>>>((const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC);
+  B200_REQUIRE((size_t)B * NC * 4 <= 40 * 1024, "head wgrad: batch %d too large for the staged dlogits", B);
+  head_wgrad_kernel<16><<<cdiv(D, 8), 256, (size_t)B * NC * sizeof(float), (cudaStream_t)stream>>>((const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, int B, int HP, int WP,
-                         int C, void* stream) {
+int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, float* dbias, int B, int HP,
+                         int WP, int C, void* stream) {
   const long long total = (long long)B * HP * WP * C;
-  unpool_relu_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)dpool, (const bf16*)pooled, argmax,
-                                                                                 (bf16*)dy, HP, WP, C, total);
+  int grid = grid_for(total, 256, 148 * 4);
+  if (dbias && 256 % C != 0) {
+    // keep the stride a multiple of C so a thread never changes channel
+    while (grid > 1 && (256LL * grid) % C != 0) --grid;
+    B200_REQUIRE((256LL * grid) % C == 0, "unpool: cannot build a channel-stable stride for C=%d", C);
+  }
+  unpool_relu_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)dpool, (const bf16*)pooled, argmax, (bf16*)dy, dbias,
+                                                                 HP, WP, C, total);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -16,7 +16,7 @@ extern "C" {
 
 #define B200_MAX_RANKS 8
 #define B200_MAX_CHANNELS 16
-#define B200_MAX_COMM_BLOCKS 64
+#define B200_MAX_COMM_BLOCKS 296
 #define B200_MAX_RANGES 4
 #define B200_MAX_SEGMENTS 32
 
@@ -74,8 +74,9 @@ int b200_head_fwd_bwd(float* z, const void* b1_bf16, const void* w2_bf16, const 
 int b200_head_wgrad(const void* h_bf16, const void* dz_bf16, const float* dlogits, float* dw2, float* db2, float* db1,
                     int B, int D, int NC, void* stream);
 /* max-pool 2x2/2 backward fused with the ReLU mask: dy[b,2h+i,2w+j,c] */
+/* dbias (may be NULL) accumulates sum_{b,h,w} dy[b,h,w,c]: the bias gradient of the convolution that produced `pooled` */
 int b200_unpool_relu_bwd(const void* dpool_bf16, const void* pooled_bf16, const uint8_t* argmax, void* dy_bf16,
-                         int B, int HP, int WP, int C, void* stream);
+                         float* dbias, int B, int HP, int WP, int C, void* stream);
 int b200_maxpool_fwd(const void* in_bf16, void* out_bf16, uint8_t* argmax, int B, int H, int W, int C, void* stream);
 /* direct convolution fallbacks (any k, stride 1), NHWC bf16, fp32 accumulate */
 int b200_conv_direct_fwd(const void* in, const void* w, const void* bias, void* out, int B, int H, int W, int Ci,

@@ -28,7 +28,7 @@ def _check(C, ref, Kd):
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
-@pytest.mark.parametrize("M,N,Kd,bn", [(128, 128, 64, 128), (128, 1024, 3136, 64), (3136, 1024, 128, 128), (100, 192, 200, 64), (256, 256, 512, 256)])
+@pytest.mark.parametrize("M,N,Kd,bn", [(128, 128, 64, 128), (128, 1024, 3136, 64), (3136, 1024, 128, 128), (104, 192, 200, 64), (256, 256, 512, 256)])
 def test_gemm_tc_all_majors(a_mn, b_mn, M, N, Kd, bn):
     torch.manual_seed(M + N + Kd)
     A, Bm = _mk(M, N, Kd, a_mn, b_mn)
@@ -68,3 +68,6 @@ def test_gemm_tc_argument_errors():
         K.gemm_tc(A, A, C, 128, 128, 64, split_k=2, out_mode=0)
     with pytest.raises(K.B200Error):
         K.gemm_tc(A, A, C, 128, 128, 64, block_n=20)
+    At = torch.zeros(64, 100, device="cuda", dtype=bf16)         # MN-major A with a pitch that is not 16-byte aligned
+    with pytest.raises(K.B200Error):
+        K.gemm_tc(At, A, C, 100, 128, 64, a_mn_major=True)

@@ -108,12 +108,14 @@ def test_pool_and_unpool():
     assert torch.equal(out.float(), ref.permute(0, 2, 3, 1))
     dp = torch.randn(B, 7, 7, Cc, device="cuda").to(bf16)
     dy = torch.empty(B, H, W, Cc, device="cuda", dtype=bf16)
-    K.unpool_relu_bwd(dp, out, am, dy)
+    db = torch.zeros(Cc, device="cuda")
+    K.unpool_relu_bwd(dp, out, am, dy, db)
     (ref * dp.float().permute(0, 3, 1, 2)).sum().backward()
     mask = (x.float() > 0)                                         # relu' on the pre-pool activation
     want = (xr.grad.permute(0, 2, 3, 1)) * mask
     # ties (exact zeros) carry no gradient in either implementation because of the relu mask
     assert torch.allclose(dy.float(), want.to(bf16).float())
+    assert torch.allclose(db, dy.float().sum((0, 1, 2)), rtol=1e-3, atol=1e-2)
 
 
 @pytest.mark.parametrize("k,pad,Ci,Co,H", [(5, 2, 32, 64, 14), (3, 0, 8, 16, 12), (3, 1, 16, 8, 9)])
