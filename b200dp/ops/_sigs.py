@@ -26,6 +26,7 @@ _SIGS = {
     "b200_allgather_slices": (I, [P, I, I, I, I, SZ, LL, P]),
     "b200_adasum_scratch_bytes": (SZ, [I, I]),
     "b200_adasum_level": (I, [P, I, I, I, I, SZ, I, SZ, I, SZ, I, PLL, PLL, P]),
+    "b200_adasum_pair_static": (I, [P, P, P, I, I, PLL, PLL, P]),
     "b200_conv1_pool_fwd": (I, [P, P, P, P, P, I, I, P, I, P, P, I, P]),
     "b200_conv1_wgrad": (I, [P, P, P, P, P, P, I, I, P]),
     "b200_head_fwd_bwd": (I, [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, I, U64, P, I, I, I, P]),

@@ -22,6 +22,7 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -675,3 +676,150 @@ int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cu
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// b200_adasum_pair_static — the one entry point of this library that allocates nothing.
+//
+// It computes the same pairwise Adasum combination as one level of b200_adasum_level
+//     out = (1 - a.b / (2|a|^2)) a + (1 - a.b / (2|b|^2)) b        per tensor segment
+// for two fp32 vectors the caller already holds (plain device pointers, or peer pointers it mapped itself).
+// The per-block partial dot products, which b200_adasum_level keeps in caller-provided segment memory, live
+// here in a fixed array compiled into the library image.
+//
+// Who needs this: code that runs INSIDE somebody else's memory regime and therefore must not, or cannot, call
+// cudaMalloc — a gradient hook plugged into a framework whose caching allocator already owns the whole
+// device (a fresh cudaMalloc fails there, or succeeds only by fragmenting the pool), a serving process that
+// carved up its memory budget at start-up, or a latency-sensitive loop that cannot afford the device-wide
+// synchronisation cudaMalloc/cudaFree imply.  Such callers cannot create a communicator (its segments are
+// cudaMalloc'ed) just to obtain a few kilobytes of scratch.
+//
+// Cost and limits: the scratch array is B200_ADASUM_STATIC_MAX_BLOCKS x B200_MAX_SEGMENTS x 3 doubles = 48 KiB
+// of device memory on EVERY GPU that loads this library, held until the process exits, used or not.
+// Requests beyond those maxima are rejected with an error, never truncated.
+//
+// Sharing: all calls on a device use the same array.  It keeps whatever the previous call left in it; that is
+// harmless because the first kernel overwrites every slot the second kernel reads (nothing has to start at
+// zero), but it also means two calls whose kernels overlap on the GPU (different streams, or different host
+// threads without ordering) race on the scratch and produce garbage.  Serialise them on one stream.
+//
+// Set-up: the array's name is only a host-side handle; the device address is looked up with
+// cudaGetSymbolAddress once per device, on the first call made while that device is current, and cached.
+// Make that first call during start-up, before any stream capture is begun.
+// =====================================================================================================
+namespace {
+
+constexpr int STATIC_MAX_BLOCKS = B200_ADASUM_STATIC_MAX_BLOCKS;
+constexpr int STATIC_SCRATCH_DOUBLES = STATIC_MAX_BLOCKS * B200_MAX_SEGMENTS * 3;
+
+static __device__ __align__(256) double g_adasum_static_scratch[STATIC_SCRATCH_DOUBLES];
+
+struct PairArgs {
+  const float* a;
+  const float* b;
+  float* out;
+  double* partials;           // device address of g_adasum_static_scratch
+  int nseg;
+  long long seg_start[B200_MAX_SEGMENTS];
+  long long seg_numel[B200_MAX_SEGMENTS];
+};
+
+// Same block/thread -> element mapping and the same reduction order as adasum_dots_kernel, so the result
+// matches b200_adasum_level bit for bit; no barrier, because both vectors are already complete.
+__global__ void __launch_bounds__(256) adasum_pair_dots_kernel(const PairArgs p) {
+  const int bid = blockIdx.x;
+  __shared__ double red[3][8];
+  for (int s = 0; s < p.nseg; ++s) {
+    double dab = 0, daa = 0, dbb = 0;
+    const float* pa = p.a + p.seg_start[s];
+    const float* pb = p.b + p.seg_start[s];
+    for (long long i = (long long)bid * blockDim.x + threadIdx.x; i < p.seg_numel[s]; i += (long long)gridDim.x * blockDim.x) {
+      const double x = pa[i], y = pb[i];
+      dab += x * y; daa += x * x; dbb += y * y;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      dab += __shfl_xor_sync(0xffffffffu, dab, o);
+      daa += __shfl_xor_sync(0xffffffffu, daa, o);
+      dbb += __shfl_xor_sync(0xffffffffu, dbb, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { red[0][w] = dab; red[1][w] = daa; red[2][w] = dbb; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      double t = 0;
+      for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += red[threadIdx.x][k];
+      p.partials[((size_t)bid * p.nseg + s) * 3 + threadIdx.x] = t;     // every slot read later is written here
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) adasum_pair_combine_kernel(const PairArgs p, int nblk_dots) {
+  __shared__ float ca_s[B200_MAX_SEGMENTS], cb_s[B200_MAX_SEGMENTS];
+  if ((int)threadIdx.x < p.nseg) {
+    double dab = 0, daa = 0, dbb = 0;
+    for (int b = 0; b < nblk_dots; ++b) {
+      const double* q = p.partials + ((size_t)b * p.nseg + threadIdx.x) * 3;
+      dab += q[0]; daa += q[1]; dbb += q[2];
+    }
+    ca_s[threadIdx.x] = (float)(1.0 - (daa > 0 ? dab / (2.0 * daa) : 0.0));
+    cb_s[threadIdx.x] = (float)(1.0 - (dbb > 0 ? dab / (2.0 * dbb) : 0.0));
+  }
+  __syncthreads();
+  for (int s = 0; s < p.nseg; ++s) {
+    const float ca = ca_s[s], cb = cb_s[s];
+    const long long st = p.seg_start[s];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.seg_numel[s]; i += (long long)gridDim.x * blockDim.x)
+      p.out[st + i] = ca * p.a[st + i] + cb * p.b[st + i];
+  }
+}
+
+constexpr int STATIC_MAX_DEVICES = 64;
+double* g_static_scratch_addr[STATIC_MAX_DEVICES] = {};
+std::mutex g_static_scratch_mu;
+
+// Device address of the static scratch on the CURRENT device (looked up once per device).
+int static_scratch_for_current_device(double** out) {
+  int dev = -1;
+  B200_CHECK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "adasum_pair_static: device ordinal %d not supported (max %d)", dev, STATIC_MAX_DEVICES);
+  std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    double* ptr = nullptr;
+    // the symbol name is a host-side stand-in; only this call yields an address a kernel may dereference
+    B200_CHECK(cudaGetSymbolAddress((void**)&ptr, g_adasum_static_scratch));
+    B200_REQUIRE(ptr != nullptr, "adasum_pair_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    g_static_scratch_addr[dev] = ptr;
+  }
+  *out = g_static_scratch_addr[dev];
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_adasum_pair_static(const float* a, const float* b, float* out, int nblocks, int nseg,
+                                       const long long* seg_start, const long long* seg_numel, void* stream) {
+  B200_REQUIRE(a != nullptr && b != nullptr && out != nullptr, "adasum_pair_static: null vector pointer");
+  B200_REQUIRE(nblocks >= 1 && nblocks <= STATIC_MAX_BLOCKS,
+               "adasum_pair_static: nblocks %d outside [1, %d] — the built-in scratch holds partials for at most %d blocks", nblocks,
+               STATIC_MAX_BLOCKS, STATIC_MAX_BLOCKS);
+  B200_REQUIRE(nseg >= 1 && nseg <= B200_MAX_SEGMENTS,
+               "adasum_pair_static: nseg %d outside [1, %d] — the built-in scratch holds at most %d tensor segments per call", nseg,
+               B200_MAX_SEGMENTS, B200_MAX_SEGMENTS);
+  B200_REQUIRE(seg_start != nullptr && seg_numel != nullptr, "adasum_pair_static: null segment table");
+  PairArgs p;
+  memset(&p, 0, sizeof p);
+  p.a = a; p.b = b; p.out = out; p.nseg = nseg;
+  for (int i = 0; i < nseg; ++i) {
+    B200_REQUIRE(seg_start[i] >= 0 && seg_numel[i] >= 0, "adasum_pair_static: segment %d has a negative start or length", i);
+    p.seg_start[i] = seg_start[i];
+    p.seg_numel[i] = seg_numel[i];
+  }
+  int rc = static_scratch_for_current_device(&p.partials);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  adasum_pair_dots_kernel<<<nblocks, 256, 0, st>>>(p);
+  B200_LAUNCH_CHECK();
+  adasum_pair_combine_kernel<<<nblocks * 2, 256, 0, st>>>(p, nblocks);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

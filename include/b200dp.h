@@ -19,6 +19,7 @@ extern "C" {
 #define B200_MAX_COMM_BLOCKS 296
 #define B200_MAX_RANGES 4
 #define B200_MAX_SEGMENTS 32
+#define B200_ADASUM_STATIC_MAX_BLOCKS 64
 
 typedef void* b200_comm_t;
 
@@ -54,6 +55,17 @@ size_t b200_adasum_scratch_bytes(int nblocks, int nseg);
 int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cur_seg, size_t cur_off, int next_seg,
                       size_t next_off, int scratch_seg, size_t scratch_off, int nseg, const long long* seg_start,
                       const long long* seg_numel, void* stream);
+
+/* No counterpart in the reference (added for callers of this library, not taken from upstream).
+ * Pairwise Adasum of two fp32 vectors, out = adasum(a, b) per segment — the same arithmetic as one
+ * b200_adasum_level — for callers that may not allocate device memory: it needs no communicator and calls no
+ * cudaMalloc/cudaFree; its scratch is a 48 KiB array built into the library (resident on every GPU that loads
+ * it, until exit).  Limits: nblocks <= B200_ADASUM_STATIC_MAX_BLOCKS, nseg <= B200_MAX_SEGMENTS; larger requests
+ * fail with an error.  All calls on a device share that scratch: run them on one stream, never overlapping.
+ * The first call on each device resolves the scratch address (cudaGetSymbolAddress) — make it before any stream
+ * capture starts. */
+int b200_adasum_pair_static(const float* a, const float* b, float* out, int nblocks, int nseg,
+                            const long long* seg_start, const long long* seg_numel, void* stream);
 
 /* ---- model kernels, CUDA-core family (first conv, head, fallbacks) ---- */
 /* conv 5x5 SAME Cin=1 + bias + ReLU + maxpool2 (horovod/tensorflow_mnist.py:49-53). step_ptr (may be NULL)
