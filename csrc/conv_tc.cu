@@ -12,6 +12,8 @@
 //
 // Replaces cuDNN's conv2d fwd/dgrad/wgrad behind layers.conv2d (horovod/tensorflow_mnist.py:49-60;
 // horovod/tensorflow_mnist_gpu.py:47-56) — SURVEY §2.5a K5, K6, K13.
+#include <stdlib.h>
+
 #include "../include/b200dp.h"
 #include "tc_sm100.cuh"
 
@@ -69,15 +71,15 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int tap = kb / p.kc_blocks, cb = kb % p.kc_blocks;
-        const int kh = tap / p.k, kw = tap % p.k;
-        const int dh = p.mode == 0 ? kh - p.pad : p.pad - kh;
-        const int dw = p.mode == 0 ? kw - p.pad : p.pad - kw;
-        mbar_wait(empty + stage, phase ^ 1, 11);
+    const bool leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    int tap = 0, cb = 0, kh = 0, kw = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int dh = p.mode == 0 ? kh - p.pad : p.pad - kh;
+      const int dw = p.mode == 0 ? kw - p.pad : p.pad - kw;
+      mbar_wait(empty + stage, phase ^ 1, 11);
+      if (leader) {
         uint8_t* sA = smem + stage * stage_bytes;
         uint8_t* sB = sA + a_bytes;
         mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + b_bytes));
@@ -90,29 +92,33 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
           // rows = ci (this CTA's N), cols = co block: K-major B
           tma_load_2d(sB, &tmB, full + stage, cb * p.KC, tap * p.Ci + n0);
         }
-        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++cb == p.kc_blocks) { cb = 0; ++tap; if (++kw == p.k) { kw = 0; ++kh; } }
+      if (++stage == p.nstage) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, p.BN, 0, p.mode == 0 ? 1 : 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < nkb; ++kb) {
-        mbar_wait(full + stage, phase, 12);
-        tc_fence_after();
-        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
-        const uint32_t sB = sA + a_bytes;
-        for (int ks = 0; ks < p.KC / 16; ++ks) {
-          const uint64_t ad = make_smem_desc(sA + ks * 32, 16, 8 * row_bytes, swz);
-          const uint64_t bd = p.mode == 0 ? make_smem_desc(sB + ks * 2048, p.KC * 128, 1024, SW_128B)
-                                          : make_smem_desc(sB + ks * 32, 16, 8 * row_bytes, swz);
-          umma_bf16(tmem_base, ad, bd, idesc, (kb > 0 || ks > 0) ? 1u : 0u);
-        }
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(128, p.BN, 0, p.mode == 0 ? 1 : 0);
+    const uint64_t a_hi = make_smem_desc(0, 16, 8 * row_bytes, swz);
+    const uint64_t b_hi = p.mode == 0 ? make_smem_desc(0, p.KC * 128, 1024, SW_128B) : make_smem_desc(0, 16, 8 * row_bytes, swz);
+    const uint32_t b_step = (p.mode == 0 ? 2048u : 32u) >> 4;
+    const uint32_t s0 = (smem_u32(smem) & 0x3FFFFu) >> 4, stage_step = (uint32_t)stage_bytes >> 4;
+    const int ksteps = p.KC / 16;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(full + stage, phase, 12);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t a_lo = s0 + stage * stage_step, b_lo = a_lo + ((uint32_t)a_bytes >> 4);
+        for (int ks = 0; ks < ksteps; ++ks)
+          umma_bf16(tmem_base, a_hi + (a_lo + ks * 2u), b_hi + (b_lo + ks * b_step), idesc, (kb > 0 || ks > 0) ? 1u : 0u);
         umma_commit(empty + stage);
         if (kb == nkb - 1) umma_commit(tmem_full);
-        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == p.nstage) { stage = 0; phase ^= 1; }
     }
   } else {
     mbar_wait(tmem_full, 0, 13);
@@ -220,12 +226,13 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_cons
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = t0; t < t1; ++t) {
-        const int img = t / p.tiles_h, h0 = (t % p.tiles_h) * TILE_H;
-        mbar_wait(empty + stage, phase ^ 1, 21);
+    const bool leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t0; t < t1; ++t) {
+      const int img = t / p.tiles_h, h0 = (t % p.tiles_h) * TILE_H;
+      mbar_wait(empty + stage, phase ^ 1, 21);
+      if (leader) {
         uint8_t* sA = smem + stage * stage_bytes;
         uint8_t* sB = sA + a_bytes;
         mbar_arrive_expect_tx(full + stage, (uint32_t)(npair_here * box_bytes + b_bytes));
@@ -236,31 +243,34 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_cons
           tma_load_4d(sA + j * box_bytes, &tmIn, full + stage, cb * p.CB, kw - p.pad, h0 + kh - p.pad, img);
         }
         for (int j = 0; j < p.BN / 64; ++j) tma_load_4d(sB + j * (TILE_PIX * 128), &tmDy, full + stage, n0 + 64 * j, 0, h0, img);
-        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == p.nstage) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, p.BN, 1, 1);
-      const uint32_t a_swz = p.CB == 64 ? SW_128B : SW_64B;
-      const int a_row = p.CB * 2;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = t0; t < t1; ++t) {
-        mbar_wait(full + stage, phase, 22);
-        tc_fence_after();
-        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
-        const uint32_t sB = sA + a_bytes;
-        for (int ks = 0; ks < TILE_PIX / 16; ++ks) {
-          // 16 pixels (K) per instruction = two 8-row swizzle atoms
-          const uint64_t ad = make_smem_desc(sA + ks * 16 * a_row, box_bytes, 8 * a_row, a_swz);
-          const uint64_t bd = make_smem_desc(sB + ks * 2048, TILE_PIX * 128, 1024, SW_128B);
-          umma_bf16(tmem_base, ad, bd, idesc, (t > t0 || ks > 0) ? 1u : 0u);
-        }
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(128, p.BN, 1, 1);
+    const uint32_t a_swz = p.CB == 64 ? SW_128B : SW_64B;
+    const int a_row = p.CB * 2;
+    const uint64_t a_hi = make_smem_desc(0, box_bytes, 8 * a_row, a_swz);
+    const uint64_t b_hi = make_smem_desc(0, TILE_PIX * 128, 1024, SW_128B);
+    const uint32_t a_step = (uint32_t)(16 * a_row) >> 4, b_step = 2048u >> 4;
+    const uint32_t s0 = (smem_u32(smem) & 0x3FFFFu) >> 4, stage_step = (uint32_t)stage_bytes >> 4;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t0; t < t1; ++t) {
+      mbar_wait(full + stage, phase, 22);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t a_lo = s0 + stage * stage_step, b_lo = a_lo + ((uint32_t)a_bytes >> 4);
+#pragma unroll
+        for (int ks = 0; ks < TILE_PIX / 16; ++ks)      // 16 pixels (K) per instruction = two 8-row swizzle atoms
+          umma_bf16(tmem_base, a_hi + (a_lo + ks * a_step), b_hi + (b_lo + ks * b_step), idesc, (t > t0 || ks > 0) ? 1u : 0u);
         umma_commit(empty + stage);
         if (t == t1 - 1) umma_commit(tmem_full);
-        if (++stage == p.nstage) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == p.nstage) { stage = 0; phase ^= 1; }
     }
   } else {
     mbar_wait(tmem_full, 0, 23);
@@ -366,16 +376,32 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
 
 }  // namespace
 
+int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H,
+                          int W, int Ci, int Co, int k, int relu, int pool, cudaStream_t st);
+
+static bool halo_enabled() {
+  const char* e = getenv("B200DP_CONV_HALO");
+  return !(e && e[0] == '0');
+}
+
 extern "C" {
 
 int b200_conv_tc_fwd(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W, int Ci,
                      int Co, int k, int relu, int pool, void* stream) {
+  if (halo_enabled()) {
+    const int rc = b200_conv_halo_launch(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
   return launch_conv(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
 }
 
 int b200_conv_tc_dgrad(const void* dout, const void* w, void* din, const void* mask_src, int B, int H, int W, int Ci, int Co,
                        int k, void* stream) {
   (void)mask_src;
+  if (halo_enabled()) {
+    const int rc = b200_conv_halo_launch(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
   return launch_conv(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
 }
 

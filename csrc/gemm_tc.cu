@@ -96,12 +96,13 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(empty + stage, phase ^ 1, 1);
+    // ===== TMA producer: the whole warp walks the loop (uniform control flow), one elected lane issues =====
+    const bool leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(empty + stage, phase ^ 1, 1);
+      if (leader) {
         uint8_t* sA = smem + stage * stage_bytes;
         uint8_t* sB = sA + A_TILE_BYTES;
         mbar_arrive_expect_tx(full + stage, (uint32_t)stage_bytes);
@@ -117,32 +118,34 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
         } else {
           for (int j = 0; j < p.bn / 64; ++j) tma_load_2d(sB + j * 8192, &tmB, full + stage, n0 + 64 * j, k0);
         }
-        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one thread drives the tensor core =====
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(BM, p.bn, p.a_mn, p.b_mn);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(full + stage, phase, 2);
-        tc_fence_after();
-        const uint32_t sA = smem_u32(smem + stage * stage_bytes);
-        const uint32_t sB = sA + A_TILE_BYTES;
+    // ===== MMA issuer: uniform loop, one elected lane drives the tensor core. Descriptors are a constant high
+    // word plus a running start-address field, so an issue costs a handful of (uniform-datapath) instructions.
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(BM, p.bn, p.a_mn, p.b_mn);
+    const uint64_t a_hi = p.a_mn ? make_smem_desc(0, 8192, 1024, SW_128B) : make_smem_desc(0, 16, 1024, SW_128B);
+    const uint64_t b_hi = p.b_mn ? make_smem_desc(0, 8192, 1024, SW_128B) : make_smem_desc(0, 16, 1024, SW_128B);
+    const uint32_t a_step = (p.a_mn ? 2048u : 32u) >> 4, b_step = (p.b_mn ? 2048u : 32u) >> 4;
+    const uint32_t s0 = (smem_u32(smem) & 0x3FFFFu) >> 4, stage_step = (uint32_t)stage_bytes >> 4;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(full + stage, phase, 2);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t a_lo = s0 + stage * stage_step, b_lo = a_lo + (A_TILE_BYTES >> 4);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t ad = p.a_mn ? make_smem_desc(sA + k * 2048, 8192, 1024, SW_128B)
-                                     : make_smem_desc(sA + k * 32, 16, 1024, SW_128B);
-          const uint64_t bd = p.b_mn ? make_smem_desc(sB + k * 2048, 8192, 1024, SW_128B)
-                                     : make_smem_desc(sB + k * 32, 16, 1024, SW_128B);
-          umma_bf16(tmem_base, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-        }
+        for (int k = 0; k < BK / 16; ++k)
+          umma_bf16(tmem_base, a_hi + (a_lo + k * a_step), b_hi + (b_lo + k * b_step), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         umma_commit(empty + stage);                 // frees the smem slot when these MMAs retire
         if (kb == kb1 - 1) umma_commit(tmem_full);  // accumulator complete
-        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
     }
   } else {
     // ===== epilogue: TMEM -> registers -> global =====

@@ -10,6 +10,14 @@ from b200dp.ops import kernels as K
 bf16 = torch.bfloat16
 
 
+@pytest.fixture(params=["halo", "tma_shift"], autouse=True)
+def conv_path(request, monkeypatch):
+    """Run every case through both tensor-core paths: the smem-resident persistent kernel (where the shape fits)
+    and the general shifted-TMA-box kernel."""
+    monkeypatch.setenv("B200DP_CONV_HALO", "1" if request.param == "halo" else "0")
+    return request.param
+
+
 def _err(a, b):
     return (a.float() - b.float()).abs().max().item(), b.float().abs().max().item()
 
