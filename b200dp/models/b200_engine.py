@@ -130,6 +130,7 @@ class B200Engine(Engine):
         self.master.copy_(init_flat(self.spec, seed, "cpu").to(self.device))
         K.cast_f32_to_bf16(self.master, self.w16)
         self._sharded_ranges: List[Tuple[int, int]] = []
+        self._shards_stale = False      # True once a two-shot step ran: peers' slices of master/m/v are newer than ours
 
         # ---- activations (plain device memory) --------------------------------------------
         B, dev = self.cap, self.device
@@ -365,6 +366,7 @@ class B200Engine(Engine):
             self._train_graphable(B, par)
             self._warm.add(key)
         self.global_step += 1
+        self._shards_stale = bool(self._sharded_ranges)
         slot = self.global_step % RING
         return StepResult(_LazyScalar(self._ring_read(slot, True)), _LazyScalar(self._ring_read(slot, False)), B)
 
@@ -389,6 +391,7 @@ class B200Engine(Engine):
             self._train_graphable(B, par)
             self._warm.add(key)
         self.global_step += 1
+        self._shards_stale = bool(self._sharded_ranges)
 
     @torch.no_grad()
     def eval_batch(self, x, y) -> StepResult:
@@ -419,7 +422,7 @@ class B200Engine(Engine):
     def _gather_sharded(self) -> None:
         """One-sided: pull every owner's slice of the two-shot ranges into the local fp32 state.
         Safe between steps: peers cannot start their next update before this rank joins its barrier."""
-        if self.n == 1 or not self._sharded_ranges:
+        if self.n == 1 or not self._sharded_ranges or not self._shards_stale:
             return
         torch.cuda.synchronize()
         T = self.T
@@ -432,9 +435,9 @@ class B200Engine(Engine):
                 if hi <= lo:
                     continue
                 for base in (0, T, 2 * T):
-                    peer = self.arena.view(self.seg_state, (base + st + lo) * 4, hi - lo, torch.float32, peer=r)
-                    self.arena.view(self.seg_state, (base + st + lo) * 4, hi - lo, torch.float32).copy_(peer)
+                    self.arena.pull_from_peer(self.seg_state, (base + st + lo) * 4, (hi - lo) * 4, r)
         torch.cuda.synchronize()
+        self._shards_stale = False
 
     def state(self) -> Dict[str, Any]:
         self._gather_sharded()
@@ -461,6 +464,7 @@ class B200Engine(Engine):
             self._graphs.clear()
         for gb in self.grads:
             gb.zero_()
+        self._shards_stale = False
         torch.cuda.synchronize()
 
     def broadcast_state(self, root_rank: int = 0) -> None:
@@ -478,5 +482,6 @@ class B200Engine(Engine):
             self._graphs.clear()
         self.global_step, self.seed = step, seed
         self.step_dev.fill_(self.global_step)
+        self._shards_stale = False
         torch.cuda.synchronize()
         _w.barrier()

@@ -24,6 +24,7 @@ _SIGS = {
     "b200_allreduce": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, F, P]),
     "b200_broadcast": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, P]),
     "b200_allgather_slices": (I, [P, I, I, I, I, SZ, LL, P]),
+    "b200_comm_pull_from_peer": (I, [P, I, SZ, SZ, I, P]),
     "b200_adasum_scratch_bytes": (SZ, [I, I]),
     "b200_adasum_level": (I, [P, I, I, I, I, SZ, I, SZ, I, SZ, I, PLL, PLL, P]),
     "b200_adasum_pair_static": (I, [P, P, P, I, I, PLL, PLL, P]),

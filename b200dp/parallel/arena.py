@@ -91,8 +91,11 @@ class SymmetricArena:
         return int(p)
 
     def bytes_view(self, seg: int, peer: Optional[int] = None) -> torch.Tensor:
-        """uint8 tensor aliasing a whole segment (``peer`` selects the rank's copy; in a real
-        communicator that is peer memory reachable over NVLink)."""
+        """uint8 tensor aliasing a whole segment.  ``peer`` selects another rank's copy — only meaningful in an
+        emulated communicator (all copies on this GPU); real peer memory is reached by kernels and by
+        :meth:`pull_from_peer`, never through torch tensors (torch would snapshot foreign-device memory)."""
+        if peer is not None and peer != self.rank and not self.emulated:
+            raise K.B200Error("peer views exist only in emulated communicators; use pull_from_peer()")
         key = (seg, self.rank if peer is None else peer)
         v = self._views.get(key)
         if v is None:
@@ -247,6 +250,11 @@ class SymmetricArena:
             raise K.B200Error(f"at most {lim} tensors per fused Adasum call")
         res = self.adasum_levels(self._staging, ping, pong, scratch, starts, seg_numel)
         flat.copy_(self.view(self._staging, res, n, torch.float32))
+
+    def pull_from_peer(self, seg: int, off: int, nbytes: int, peer: int) -> None:
+        """One-sided: local[off:off+nbytes] = peer[off:off+nbytes] (cudaMemcpy over the IPC mapping)."""
+        K.check(K.lib().b200_comm_pull_from_peer(self.h, seg, off, nbytes, peer,
+                                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "pull_from_peer")
 
     def allgather_slices_(self, seg: int, off: int, numel: int, nblocks: int = 16) -> None:
         K.check(K.lib().b200_allgather_slices(self.h, CH_GATHER, nblocks, 512, seg, off, numel,

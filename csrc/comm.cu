@@ -626,6 +626,19 @@ int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads,
   return launch_ranked(c, args, copy_collective_kernel<false>, copy_collective_kernel<true>, nblocks, nthreads, (cudaStream_t)stream, 1);
 }
 
+// One-sided pull: copy [off, off+bytes) of `peer`'s copy of a segment into the same place of the local copy
+// (rank 0 uses it to collect the owner-sharded Adam state when it checkpoints alone).
+int b200_comm_pull_from_peer(b200_comm_t h, int seg, size_t off, size_t bytes, int peer, void* stream) {
+  Comm* c = (Comm*)h;
+  int rc;
+  if ((rc = check_seg(c, seg, off, bytes, "pull_from_peer"))) return rc;
+  B200_REQUIRE(peer >= 0 && peer < c->n, "peer %d outside world of %d", peer, c->n);
+  const int me = c->emulated ? 0 : c->rank;
+  if (peer == me || bytes == 0) return B200_OK;
+  B200_CHECK(cudaMemcpyAsync(seg_ptr(c, seg, me, off), seg_ptr(c, seg, peer, off), bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  return B200_OK;
+}
+
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg) { return (size_t)nblocks * nseg * 3 * sizeof(double); }
 
 // One Adasum level: next = combine(cur[lower], cur[higher]) for partner = rank ^ (1 << level).

@@ -50,6 +50,9 @@ int b200_broadcast(b200_comm_t h, int channel, int nblocks, int nthreads, int ro
                    int dst_seg, size_t dst_off, long long numel, void* stream);
 int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads, int seg, size_t off, long long numel,
                           void* stream);
+/* one-sided copy of a peer's [off, off+bytes) into the same range of the local segment (rank-0 checkpoint gather,
+ * horovod/tensorflow_mnist.py:157-159: only worker 0 saves) */
+int b200_comm_pull_from_peer(b200_comm_t h, int seg, size_t off, size_t bytes, int peer, void* stream);
 /* hvd.Adasum (horovod/tensorflow_mnist.py:133), one tree level per call */
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg);
 int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cur_seg, size_t cur_off, int next_seg,

@@ -20,6 +20,9 @@ def _run(np_, algo, tmp_path):
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-4000:])
     res = [json.load(open(p)) for p in sorted(glob.glob(str(tmp_path / "r*.json")))]
     assert len(res) == np_
+    art = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(art):
+        json.dump(res, open(os.path.join(art, f"multi_{np_}_{algo}.json"), "w"), indent=1)
     return res
 
 

@@ -76,6 +76,10 @@ if r == 0:
         moved = (oracle.params.data - init)
         cos = torch.nn.functional.cosine_similarity(st["tensors"]["params"].cuda() - init, moved, dim=0).item()
         res["oracle_cos"] = cos
+        half = spec.total // 2
+        got_mv = st["tensors"]["params"].cuda() - init
+        res["oracle_cos_halves"] = [torch.nn.functional.cosine_similarity(got_mv[:half], moved[:half], dim=0).item(),
+                                    torch.nn.functional.cosine_similarity(got_mv[half:], moved[half:], dim=0).item()]
         res["oracle_max_diff"] = float(d.abs().max())
         res["adam_m_cos"] = torch.nn.functional.cosine_similarity(st["tensors"]["adam_m"].cuda(), oracle.m, dim=0).item()
     res["ckpt_step"] = st["meta"]["global_step"]
