@@ -16,6 +16,7 @@ weights, step counter, hyper-parameters, loss ring) lives in symmetric peer-mapp
 """
 from __future__ import annotations
 
+import ctypes
 import os
 from typing import Any, Dict, List, Optional, Tuple, Union
 
@@ -113,8 +114,13 @@ class B200Engine(Engine):
         a = self.arena
         self.seg_ctrl = a.alloc(CTRL_BYTES)
         self.seg_state = a.alloc(T * 4 * 3)
-        self.seg_grad = a.alloc(T * 4 * 3 + (1 << 16))       # parity 0, parity 1, adasum pong, adasum scratch
-        self.seg_w16 = a.alloc(T * 2)
+        d0 = _as_dist_adam(optimizer)
+        want = os.environ.get("B200DP_ALLREDUCE_ALGO") or (d0.algo if d0 else "auto")
+        self.nvls = bool(self.n > 1 and want in ("nvls", "auto") and a.nvls_supported()
+                         and (want == "nvls" or autoselect.nvls_min_bytes(self.n) is not None))
+        galloc = a.alloc_multicast if self.nvls else a.alloc
+        self.seg_grad = galloc(T * 4 * 3 + (1 << 16))        # parity 0, parity 1, adasum pong, adasum scratch
+        self.seg_w16 = galloc(T * 2)
         self.master = a.view(self.seg_state, 0, T, torch.float32)
         self.m = a.view(self.seg_state, T * 4, T, torch.float32)
         self.v = a.view(self.seg_state, 2 * T * 4, T, torch.float32)
@@ -186,8 +192,8 @@ class B200Engine(Engine):
         self._sharded_ranges = []
 
         def rng(b):
-            algo = autoselect.choose(b.numel * 4, self.n, forced) if (self.reduce and not adasum) else 0
-            if algo == autoselect.TWOSHOT:
+            algo = autoselect.choose(b.numel * 4, self.n, forced, nvls_ok=self.nvls) if (self.reduce and not adasum) else 0
+            if algo in (autoselect.TWOSHOT, autoselect.NVLS):
                 self._sharded_ranges.append((b.start, b.numel))
             return (b.start, b.numel, algo, 1)
         by = {b.name: b for b in buckets}
@@ -295,13 +301,25 @@ class B200Engine(Engine):
     def _comm(self, channel: int, ranges, par: int, *, reduce: Optional[bool] = None, grad_off: Optional[int] = None,
               scale: Optional[float] = None) -> None:
         T4 = self.T * 4
-        nb = self.comm_blocks if sum(r[1] for r in ranges) >= (1 << 20) else 16
+        red = self.reduce if reduce is None else reduce
+        sc = self.scale if scale is None else scale
+        cur = par * T4 if grad_off is None else grad_off
+        p2p = [r for r in ranges if r[2] != autoselect.NVLS or not red]
+        for r in ranges:
+            if r[2] == autoselect.NVLS and red:
+                # in-switch reduction of the range (multimem.ld_reduce), Adam on the owned slice, multicast bf16 store
+                K.check(K.lib().b200_fused_allreduce_adam_nvls(
+                    self.arena.h, channel + 8, self.comm_blocks if r[1] >= (1 << 20) else 16, 512, self.seg_grad, cur,
+                    (1 - par) * T4, self.seg_state, 0, T4, 2 * T4, self.seg_w16, 0, self.seg_ctrl, CTRL_STEP, CTRL_HYPER,
+                    float(sc), r[0], r[1], r[3], ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "fused_nvls")
+        if not p2p:
+            return
+        nb = self.comm_blocks if sum(r[1] for r in p2p) >= (1 << 20) else 32
         self.arena.fused_allreduce_adam(
-            channel=channel, nblocks=nb, nthreads=512, reduce=self.reduce if reduce is None else reduce,
-            grad_seg=self.seg_grad, grad_cur_off=par * T4 if grad_off is None else grad_off, grad_other_off=(1 - par) * T4,
+            channel=channel, nblocks=nb, nthreads=512, reduce=red,
+            grad_seg=self.seg_grad, grad_cur_off=cur, grad_other_off=(1 - par) * T4,
             state_seg=self.seg_state, master_off=0, m_off=T4, v_off=2 * T4, w16_seg=self.seg_w16, w16_off=0,
-            ctrl_seg=self.seg_ctrl, step_off=CTRL_STEP, hyper_off=CTRL_HYPER,
-            scale=self.scale if scale is None else scale, ranges=ranges)
+            ctrl_seg=self.seg_ctrl, step_off=CTRL_STEP, hyper_off=CTRL_HYPER, scale=sc, ranges=p2p)
 
     def _adasum_update(self, par: int) -> None:
         T4 = self.T * 4

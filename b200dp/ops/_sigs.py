@@ -25,6 +25,13 @@ _SIGS = {
     "b200_broadcast": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, P]),
     "b200_allgather_slices": (I, [P, I, I, I, I, SZ, LL, P]),
     "b200_comm_pull_from_peer": (I, [P, I, SZ, SZ, I, P]),
+    "b200_nvls_supported": (I, []),
+    "b200_comm_mcseg_alloc": (I, [P, SZ, PI, PI, PI, C.POINTER(SZ)]),
+    "b200_comm_mcseg_open": (I, [P, I, PI, I]),
+    "b200_comm_mcseg_bind": (I, [P, I]),
+    "b200_comm_seg_mc_ptr": (P, [P, I]),
+    "b200_allreduce_nvls": (I, [P, I, I, I, I, SZ, I, SZ, LL, F, P]),
+    "b200_fused_allreduce_adam_nvls": (I, [P, I, I, I, I, SZ, SZ, I, SZ, SZ, SZ, I, SZ, I, SZ, SZ, F, LL, LL, I, P]),
     "b200_adasum_scratch_bytes": (SZ, [I, I]),
     "b200_adasum_level": (I, [P, I, I, I, I, SZ, I, SZ, I, SZ, I, PLL, PLL, P]),
     "b200_adasum_pair_static": (I, [P, P, P, I, I, PLL, PLL, P]),

@@ -84,6 +84,59 @@ class SymmetricArena:
         self.seg_bytes.append(nbytes)
         return seg.value
 
+    # ------------------------------------------------------------------ NVLS (multicast) segments
+    def nvls_supported(self) -> bool:
+        return (not self.emulated) and self.n > 1 and bool(K.lib().b200_nvls_supported())
+
+    def _exchange_fds(self, mine: List[int]) -> List[List[int]]:
+        """All-to-all of POSIX file descriptors over AF_UNIX + SCM_RIGHTS (abstract socket names, no files)."""
+        import socket
+        self._fdx_round = getattr(self, "_fdx_round", 0) + 1
+        base = f"\0b200dp-{os.environ.get('MASTER_PORT', '0')}-{self._fdx_round}"
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(f"{base}-{self.rank}")
+        srv.listen(self.n)
+        dist.barrier()
+        for p in range(self.n):
+            if p == self.rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(f"{base}-{p}")
+            socket.send_fds(c, [bytes([self.rank])], list(mine))
+            c.close()
+        got: List[List[int]] = [[] for _ in range(self.n)]
+        got[self.rank] = list(mine)
+        for _ in range(self.n - 1):
+            conn, _ = srv.accept()
+            msg, fds, _, _ = socket.recv_fds(conn, 16, 8)
+            got[msg[0]] = list(fds)
+            conn.close()
+        srv.close()
+        dist.barrier()
+        return got
+
+    def alloc_multicast(self, nbytes: int) -> int:
+        """Collective: a symmetric segment bound to an NVSwitch multicast object (plus the usual peer mappings)."""
+        if not self.nvls_supported():
+            raise K.B200Error("NVLS multicast is not supported by this device/driver/world")
+        seg, mem_fd, mc_fd = ctypes.c_int(-1), ctypes.c_int(-1), ctypes.c_int(-1)
+        actual = ctypes.c_size_t(0)
+        K.check(K.lib().b200_comm_mcseg_alloc(self.h, _round_up(int(nbytes), 256), ctypes.byref(seg), ctypes.byref(mem_fd),
+                                              ctypes.byref(mc_fd), ctypes.byref(actual)), "mcseg_alloc")
+        mine = [mem_fd.value] + ([mc_fd.value] if self.rank == 0 else [])
+        got = self._exchange_fds(mine)
+        mem_fds = (ctypes.c_int * self.n)(*[g[0] if g else -1 for g in got])
+        K.check(K.lib().b200_comm_mcseg_open(self.h, seg.value, mem_fds, got[0][1] if self.rank != 0 else -1), "mcseg_open")
+        os.close(mem_fd.value)
+        if self.rank == 0:
+            os.close(mc_fd.value)
+        dist.barrier()                       # every device joined the team before anyone binds
+        K.check(K.lib().b200_comm_mcseg_bind(self.h, seg.value), "mcseg_bind")
+        dist.barrier()
+        self.seg_bytes.append(int(actual.value))
+        self.mc_segs = getattr(self, "mc_segs", set()) | {seg.value}
+        return seg.value
+
     def ptr(self, seg: int, peer: Optional[int] = None) -> int:
         p = K.lib().b200_comm_seg_ptr(self.h, seg, self.rank if peer is None else peer)
         if not p:

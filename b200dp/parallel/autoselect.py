@@ -50,16 +50,45 @@ def crossover_bytes(nranks: int) -> int:
     return t[keys[-1]]
 
 
-def choose(nbytes: int, nranks: int, forced: Optional[str] = None) -> int:
+_nvls_min: Optional[Dict[int, int]] = None
+
+
+def nvls_min_bytes(nranks: int) -> Optional[int]:
+    """Message size from which the in-switch (NVLS) reduction beats two-shot, if a sweep recorded one."""
+    global _nvls_min
+    if _nvls_min is None:
+        _nvls_min = {}
+        here = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        for p in (os.environ.get("B200DP_ALLREDUCE_TABLE"), os.path.join(here, "profiles", "allreduce_table.json")):
+            if p and os.path.exists(p):
+                try:
+                    for k, v in json.load(open(p)).get("nvls_min_bytes", {}).items():
+                        _nvls_min[int(k)] = int(v)
+                    break
+                except (OSError, ValueError):
+                    pass
+    return _nvls_min.get(nranks)
+
+
+def choose(nbytes: int, nranks: int, forced: Optional[str] = None, nvls_ok: bool = False) -> int:
     forced = forced or os.environ.get("B200DP_ALLREDUCE_ALGO")
-    if forced and forced != "auto":
-        a = _NAMES[forced]
-        return TWOSHOT if a == NVLS else a
     if nranks <= 1:
         return ONESHOT
-    return ONESHOT if nbytes <= crossover_bytes(nranks) else TWOSHOT
+    if forced and forced != "auto":
+        a = _NAMES[forced]
+        if a == NVLS:
+            # tiny ranges stay one-shot (a multicast round trip buys nothing below the latency floor)
+            return NVLS if (nvls_ok and nbytes >= (1 << 16)) else (TWOSHOT if nbytes > crossover_bytes(nranks) else ONESHOT)
+        return a
+    if nbytes <= crossover_bytes(nranks):
+        return ONESHOT
+    mn = nvls_min_bytes(nranks)
+    if nvls_ok and mn is not None and nbytes >= mn:
+        return NVLS
+    return TWOSHOT
 
 
 def reset() -> None:
-    global _table
+    global _table, _nvls_min
     _table = None
+    _nvls_min = None

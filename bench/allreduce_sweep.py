@@ -55,6 +55,15 @@ def main():
     dst_off = maxel * 4
     src.copy_(torch.full((maxel,), float(r + 1), device=dev))
     tn = torch.empty(maxel, device=dev) if nccl is not None else None
+    seg_mc = None
+    if arena.nvls_supported():
+        try:
+            seg_mc = arena.alloc_multicast(maxel * 4 * 2 + 4096)
+            arena.view(seg_mc, 0, maxel, torch.float32).copy_(torch.full((maxel,), float(r + 1), device=dev))
+        except Exception as e:  # noqa: BLE001
+            if r == 0:
+                print(json.dumps({"nvls": "unavailable", "why": str(e)[:200]}), flush=True)
+            seg_mc = None
     stream = lambda: ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def shape(numel):
@@ -94,6 +103,16 @@ def main():
             us = timed(f, iters)
             row[name + "_us"] = us
             row[name + "_busbw_gbs"] = numel * 4 * 2 * (n - 1) / n / us / 1e3
+        if seg_mc is not None and numel * 4 >= 4096:
+            fn = lambda: K.check(K.lib().b200_allreduce_nvls(arena.h, 7, nb, nt, seg_mc, 0, seg_mc, dst_off, numel, 1.0 / n, stream()))
+            fn()
+            torch.cuda.synchronize()
+            got = arena.view(seg_mc, dst_off, numel, torch.float32)
+            want = (n + 1) / 2.0
+            assert abs(float(got[0]) - want) < 1e-5 and abs(float(got[numel - 1]) - want) < 1e-5, ("nvls", S, float(got[0]), want)
+            us = timed(fn, iters)
+            row["nvls_us"] = us
+            row["nvls_busbw_gbs"] = numel * 4 * 2 * (n - 1) / n / us / 1e3
         fb = lambda: K.check(K.lib().b200_broadcast(arena.h, 6, nb, nt, 0, seg, 0, seg, dst_off, numel, stream()))
         us = timed(fb, iters)
         row["bcast_us"] = us
@@ -107,7 +126,7 @@ def main():
             row["nccl_bcast_us"] = us
             row["nccl_bcast_gbs"] = numel * 4 / us / 1e3
         # roofline: two-shot moves 2(N-1)/N*S per direction per GPU over NVLink
-        best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us"))
+        best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us", "nvls_us"))
         row["best_us"] = best
         row["nvlink_roofline_us"] = numel * 4 * 2 * (n - 1) / n / (PEER_GBS * 1e3)
         row["frac_of_roofline"] = row["nvlink_roofline_us"] / best
@@ -119,13 +138,21 @@ def main():
         for row in rows:
             if "oneshot_us" in row and row["oneshot_us"] <= row.get("twoshot_us", float("inf")):
                 cross = row["bytes"]
-        out = {"n_gpus": n, "rows": rows, "oneshot_max_bytes": cross, "peer_gbs_denominator": PEER_GBS}
+        nvls_min = None
+        for row in reversed(rows):
+            if "nvls_us" in row and row["nvls_us"] < row.get("twoshot_us", float("inf")) and row["nvls_us"] < row.get("oneshot_us", float("inf")):
+                nvls_min = row["bytes"]
+            else:
+                break
+        out = {"n_gpus": n, "rows": rows, "oneshot_max_bytes": cross, "nvls_min_bytes": nvls_min, "peer_gbs_denominator": PEER_GBS}
         os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
         json.dump(out, open(a.out, "w"), indent=1)
         if a.write_table:
             tp = os.path.join(os.path.dirname(a.out) or ".", "allreduce_table.json")
             tab = json.load(open(tp)) if os.path.exists(tp) else {"oneshot_max_bytes": {}}
             tab["oneshot_max_bytes"][str(n)] = cross
+            if nvls_min is not None:
+                tab.setdefault("nvls_min_bytes", {})[str(n)] = nvls_min
             json.dump(tab, open(tp, "w"), indent=1)
     hvd.shutdown()
 

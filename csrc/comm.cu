@@ -44,6 +44,7 @@ struct Seg {
   void* base[MAXR] = {};
   size_t bytes = 0;
   bool opened[MAXR] = {};
+  bool vmm = false;           // VMM/multicast-backed: mappings are released with the process, not with cudaFree
 };
 
 struct Comm {
@@ -118,15 +119,22 @@ __device__ __forceinline__ float adam_elem(float g, float& p, float& m, float& v
   return p;
 }
 
+// All peer loads are issued before the first add (8 independent 16-byte NVLink reads in flight per thread);
+// the sum itself runs in fixed rank order so every rank computes the same bits.
+__device__ __forceinline__ float4 reduce_ptrs(const float* const* ptrs, int n, long long i) {
+  float4 t[MAXR];
+#pragma unroll
+  for (int r = 0; r < MAXR; ++r)
+    if (r < n) t[r] = ld_f4(ptrs[r] + i);
+  float4 s = t[0];
+#pragma unroll
+  for (int r = 1; r < MAXR; ++r)
+    if (r < n) { s.x += t[r].x; s.y += t[r].y; s.z += t[r].z; s.w += t[r].w; }
+  return s;
+}
+
 __device__ __forceinline__ float4 reduce_peers(const FusedArgs& a, long long i) {
-  float4 s = ld_f4(a.grad[0] + i);
-  if (a.reduce) {
-#pragma unroll 1
-    for (int r = 1; r < a.n; ++r) {
-      const float4 t = ld_f4(a.grad[r] + i);
-      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
-    }
-  }
+  float4 s = reduce_ptrs(a.grad, a.reduce ? a.n : 1, i);
   s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
   return s;
 }
@@ -239,11 +247,7 @@ __global__ void __launch_bounds__(512) allreduce_plain_kernel(const PlainArgs ar
   rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
   if (a.algo == 0) {
     for (long long q = tid; q < a.numel / 4; q += nthr) {
-      float4 s = ld_f4(a.src[0] + q * 4);
-      for (int r = 1; r < a.n; ++r) {
-        const float4 t = ld_f4(a.src[r] + q * 4);
-        s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
-      }
+      float4 s = reduce_ptrs(a.src, a.n, q * 4);
       s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
       st_f4(a.dst[a.rank] + q * 4, s);
     }
@@ -253,11 +257,7 @@ __global__ void __launch_bounds__(512) allreduce_plain_kernel(const PlainArgs ar
     const long long lo = min((long long)a.rank * chunk, a.numel), hi = min(lo + chunk, a.numel);
     for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
       const long long i = lo + q * 4;
-      float4 s = ld_f4(a.src[0] + i);
-      for (int r = 1; r < a.n; ++r) {
-        const float4 t = ld_f4(a.src[r] + i);
-        s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
-      }
+      float4 s = reduce_ptrs(a.src, a.n, i);
       s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
       for (int r = 0; r < a.n; ++r) st_f4(a.dst[r] + i, s);
     }
@@ -276,8 +276,33 @@ __global__ void __launch_bounds__(512) copy_collective_kernel(const PlainArgs ar
   uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
   rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
   if (mode == 0) {
-    if (a.rank != a.root || a.src[a.root] != a.dst[a.rank])
+    // Large messages: scatter + all-gather, so the root's outbound link carries ~2S instead of (N-1)S.
+    // Phase 1: rank r pulls slice r from the root (the root copies everything locally).
+    long long chunk = (a.numel + a.n - 1) / a.n;
+    chunk = (chunk + 3) / 4 * 4;
+    const bool staged = a.n > 2 && a.numel * 4 >= (1 << 20);
+    if (a.rank == a.root) {
+      if (a.src[a.root] != a.dst[a.rank])
+        for (long long q = tid; q < a.numel / 4; q += nthr) st_f4(a.dst[a.rank] + q * 4, ld_f4(a.src[a.root] + q * 4));
+    } else if (!staged) {
       for (long long q = tid; q < a.numel / 4; q += nthr) st_f4(a.dst[a.rank] + q * 4, ld_f4(a.src[a.root] + q * 4));
+    } else {
+      const long long lo = min((long long)a.rank * chunk, a.numel), hi = min(lo + chunk, a.numel);
+      for (long long q = tid; q < (hi - lo) / 4; q += nthr) st_f4(a.dst[a.rank] + lo + q * 4, ld_f4(a.src[a.root] + lo + q * 4));
+    }
+    if (staged) {
+      __threadfence_system();
+      rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+      // Phase 2: pull every other slice from the rank that owns it (the root's own slice comes from the root).
+      if (a.rank != a.root) {
+        for (int r = 0; r < a.n; ++r) {
+          if (r == a.rank) continue;
+          const long long lo = min((long long)r * chunk, a.numel), hi = min(lo + chunk, a.numel);
+          const float* from = r == a.root ? a.src[a.root] : a.dst[r];
+          for (long long q = tid; q < (hi - lo) / 4; q += nthr) st_f4(a.dst[a.rank] + lo + q * 4, ld_f4(from + lo + q * 4));
+        }
+      }
+    }
   } else {
     long long chunk = (a.numel + a.n - 1) / a.n;
     chunk = (chunk + 3) / 4 * 4;
@@ -502,7 +527,7 @@ int b200_comm_destroy(b200_comm_t h) {
   cudaDeviceSynchronize();
   for (Seg& s : c->segs)
     for (int r = 0; r < c->n; ++r) {
-      if (!s.base[r]) continue;
+      if (!s.base[r] || s.vmm) continue;
       if (c->emulated || r == c->rank) cudaFree(s.base[r]);
       else if (s.opened[r]) cudaIpcCloseMemHandle(s.base[r]);
     }
@@ -836,3 +861,373 @@ extern "C" int b200_adasum_pair_static(const float* a, const float* b, float* ou
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
+
+// =====================================================================================================
+// NVLS: symmetric segments backed by the CUDA VMM API and bound to an NVSwitch multicast object, so a kernel
+// can reduce IN the switch (multimem.ld_reduce) and broadcast THROUGH it (multimem.st).  SURVEY §5.8 / W23.
+// A multicast segment is also peer-mapped like an IPC segment, so every P2P kernel above works on it unchanged.
+//   alloc  : cuMemCreate(POSIX fd) + local map; rank 0 also cuMulticastCreate.   -> fds go to the peers (SCM_RIGHTS,
+//            done by the Python control plane)
+//   open   : import peers' memory + the multicast object, cuMulticastAddDevice
+//   (control-plane barrier: every device must be added before any memory is bound)
+//   bind   : cuMulticastBindMem(local memory) + map the multicast object
+// =====================================================================================================
+#include <cuda.h>
+#include <unistd.h>
+
+namespace {
+
+struct DriverApi {
+  CUresult (*MemCreate)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
+  CUresult (*MemRelease)(CUmemGenericAllocationHandle);
+  CUresult (*MemAddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long);
+  CUresult (*MemAddressFree)(CUdeviceptr, size_t);
+  CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long);
+  CUresult (*MemUnmap)(CUdeviceptr, size_t);
+  CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t);
+  CUresult (*MemExportToShareableHandle)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long);
+  CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType);
+  CUresult (*MemGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
+  CUresult (*MulticastCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+  CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice);
+  CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long);
+  CUresult (*MulticastGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  CUresult (*DeviceGet)(CUdevice*, int);
+  CUresult (*DeviceGetAttribute)(int*, CUdevice_attribute, CUdevice);
+  bool ok = false;
+};
+
+template <typename T>
+bool drv_sym(const char* name, T* out) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) return false;
+  *out = (T)p;
+  return true;
+}
+
+DriverApi* drv() {
+  static DriverApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    bool ok = true;
+    ok &= drv_sym("cuMemCreate", &api.MemCreate);
+    ok &= drv_sym("cuMemRelease", &api.MemRelease);
+    ok &= drv_sym("cuMemAddressReserve", &api.MemAddressReserve);
+    ok &= drv_sym("cuMemAddressFree", &api.MemAddressFree);
+    ok &= drv_sym("cuMemMap", &api.MemMap);
+    ok &= drv_sym("cuMemUnmap", &api.MemUnmap);
+    ok &= drv_sym("cuMemSetAccess", &api.MemSetAccess);
+    ok &= drv_sym("cuMemExportToShareableHandle", &api.MemExportToShareableHandle);
+    ok &= drv_sym("cuMemImportFromShareableHandle", &api.MemImportFromShareableHandle);
+    ok &= drv_sym("cuMemGetAllocationGranularity", &api.MemGetAllocationGranularity);
+    ok &= drv_sym("cuMulticastCreate", &api.MulticastCreate);
+    ok &= drv_sym("cuMulticastAddDevice", &api.MulticastAddDevice);
+    ok &= drv_sym("cuMulticastBindMem", &api.MulticastBindMem);
+    ok &= drv_sym("cuMulticastGetGranularity", &api.MulticastGetGranularity);
+    ok &= drv_sym("cuDeviceGet", &api.DeviceGet);
+    ok &= drv_sym("cuDeviceGetAttribute", &api.DeviceGetAttribute);
+    api.ok = ok;
+  });
+  return &api;
+}
+
+#define B200_DRV(expr)                                                                                  \
+  do {                                                                                                  \
+    CUresult _r = (expr);                                                                               \
+    if (_r != CUDA_SUCCESS) {                                                                           \
+      b200_set_error("%s:%d: %s -> CUresult %d", __FILE__, __LINE__, #expr, (int)_r);                   \
+      return B200_ERR_CUDA;                                                                             \
+    }                                                                                                   \
+  } while (0)
+
+struct McSeg {
+  int seg_id = -1;
+  size_t size = 0;
+  CUmemGenericAllocationHandle mem[MAXR] = {};
+  CUmemGenericAllocationHandle mc = 0;
+  void* mc_base = nullptr;
+};
+std::vector<std::pair<Comm*, McSeg>> g_mcsegs;
+std::mutex g_mc_mu;
+
+McSeg* find_mc(Comm* c, int seg) {
+  for (auto& e : g_mcsegs)
+    if (e.first == c && e.second.seg_id == seg) return &e.second;
+  return nullptr;
+}
+
+int map_rw(DriverApi* d, CUmemGenericAllocationHandle hnd, size_t size, size_t gran, int dev, void** out) {
+  CUdeviceptr va = 0;
+  B200_DRV(d->MemAddressReserve(&va, size, gran, 0, 0));
+  B200_DRV(d->MemMap(va, size, 0, hnd, 0));
+  CUmemAccessDesc acc;
+  memset(&acc, 0, sizeof acc);
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = dev;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  B200_DRV(d->MemSetAccess(va, size, &acc, 1));
+  *out = (void*)va;
+  return B200_OK;
+}
+
+// ---- kernels -------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
+  const unsigned long long x = ((unsigned long long)v.y << 32) | v.x;
+  asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(x) : "memory");
+}
+
+struct NvlsArgs {
+  int rank, n, channel, mode;      // mode 0: plain allreduce (dst = scale*sum), 1: fused Adam
+  PadPtrs pad;
+  const float* src_mc;             // multicast view of the gradient / source buffer
+  float* dst_mc;                   // mode 0: multicast view of the result buffer
+  bf16* w16_mc;                    // mode 1: multicast view of the bf16 weights
+  float* grad_other;               // mode 1: local other-parity gradient buffer (cleared)
+  float* master; float* m; float* v;
+  const int* step_ptr; const double* hyper;
+  float scale;
+  long long start, numel;
+  int zero_other;
+  unsigned long long timeout;
+};
+
+// Rank r owns slice r: the switch pulls that slice from every GPU and returns one sum (multimem.ld_reduce);
+// the owner applies scale (+Adam) and the switch replicates the store to every GPU (multimem.st).
+__global__ void __launch_bounds__(512) nvls_allreduce_kernel(const NvlsArgs a) {
+  const int bid = blockIdx.x;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  __shared__ AdamCoef coef;
+  if (a.mode == 1 && threadIdx.x == 0) {
+    const int t = *a.step_ptr;
+    const double lr = a.hyper[0], b1 = a.hyper[1], b2 = a.hyper[2], eps = a.hyper[3];
+    const double bc1 = 1.0 - pow(b1, (double)t), bc2 = 1.0 - pow(b2, (double)t);
+    coef.b1 = (float)b1; coef.b2 = (float)b2; coef.eps = (float)eps;
+    if (a.hyper[4] == 0.0) { coef.step_size = (float)(lr * sqrt(bc2) / bc1); coef.vscale = 1.f; }
+    else { coef.step_size = (float)(lr / bc1); coef.vscale = (float)(1.0 / sqrt(bc2)); }
+  }
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  const AdamCoef c = coef;
+  long long chunk = (a.numel + a.n - 1) / a.n;
+  chunk = (chunk + 3) / 4 * 4;
+  const long long lo = min((long long)a.rank * chunk, a.numel), hi = min(lo + chunk, a.numel);
+  for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
+    const long long i = a.start + lo + q * 4;
+    float4 g = multimem_ld_reduce_f4(a.src_mc + i);
+    g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+    if (a.mode == 0) {
+      multimem_st_f4(a.dst_mc + i, g);
+    } else {
+      float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+      adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+      adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+      st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+      multimem_st_b64(a.w16_mc + i, pack_bf16x4(p));
+    }
+  }
+  if (a.mode == 1 && a.zero_other)
+    for (long long q = tid; q < a.numel / 4; q += nthr) st_f4(a.grad_other + a.start + q * 4, make_float4(0.f, 0.f, 0.f, 0.f));
+  __threadfence_system();
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+}
+
+}  // namespace
+
+extern "C" {
+
+// 1 when this device can join an NVSwitch multicast team (NVLS), else 0.
+int b200_nvls_supported(void) {
+  DriverApi* d = drv();
+  if (!d->ok) return 0;
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  cudaFree(0);
+  CUdevice cd;
+  if (d->DeviceGet(&cd, dev) != CUDA_SUCCESS) return 0;
+  if (d->DeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cd) != CUDA_SUCCESS) return 0;
+  return v != 0;
+}
+
+// Step 1 (every rank): allocate the local part. mem_fd_out receives a POSIX fd of the local memory; on rank 0
+// mc_fd_out receives the fd of the freshly created multicast object (-1 elsewhere). The caller ships the fds.
+int b200_comm_mcseg_alloc(b200_comm_t h, size_t bytes, int* seg_id, int* mem_fd_out, int* mc_fd_out, size_t* actual_bytes) {
+  Comm* c = (Comm*)h;
+  DriverApi* d = drv();
+  B200_REQUIRE(d->ok, "driver VMM/multicast entry points are not available");
+  B200_REQUIRE(!c->emulated && c->n > 1, "multicast segments need a real multi-GPU communicator");
+  B200_REQUIRE(!c->segs.empty(), "allocate the signal pad (segment 0) first");
+  B200_CHECK(cudaFree(0));
+  CUmulticastObjectProp mp;
+  memset(&mp, 0, sizeof mp);
+  mp.numDevices = (unsigned)c->n;
+  mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  mp.size = bytes;
+  size_t gran = 0;
+  B200_DRV(d->MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+  CUmemAllocationProp ap;
+  memset(&ap, 0, sizeof ap);
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = c->device;
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t mgran = 0;
+  B200_DRV(d->MemGetAllocationGranularity(&mgran, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  if (mgran > gran) gran = mgran;
+  const size_t size = (bytes + gran - 1) / gran * gran;
+  mp.size = size;
+  McSeg ms;
+  ms.size = size;
+  B200_DRV(d->MemCreate(&ms.mem[c->rank], size, &ap, 0));
+  Seg s;
+  s.bytes = size;
+  s.vmm = true;
+  int rc = map_rw(d, ms.mem[c->rank], size, gran, c->device, &s.base[c->rank]);
+  if (rc) return rc;
+  B200_CHECK(cudaMemset(s.base[c->rank], 0, size));
+  B200_CHECK(cudaDeviceSynchronize());
+  int fd = -1;
+  B200_DRV(d->MemExportToShareableHandle(&fd, ms.mem[c->rank], CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  *mem_fd_out = fd;
+  *mc_fd_out = -1;
+  if (c->rank == 0) {
+    B200_DRV(d->MulticastCreate(&ms.mc, &mp));
+    int mfd = -1;
+    B200_DRV(d->MemExportToShareableHandle(&mfd, ms.mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+    *mc_fd_out = mfd;
+  }
+  c->segs.push_back(s);
+  ms.seg_id = (int)c->segs.size() - 1;
+  *seg_id = ms.seg_id;
+  if (actual_bytes) *actual_bytes = size;
+  std::lock_guard<std::mutex> lk(g_mc_mu);
+  g_mcsegs.emplace_back(c, ms);
+  return B200_OK;
+}
+
+// Step 2: mem_fds[r] = fd of rank r's memory as received in THIS process (own entry ignored); mc_fd = fd of the
+// multicast object as received here (ignored on rank 0). Imports, peer-maps, and adds this device to the team.
+int b200_comm_mcseg_open(b200_comm_t h, int seg_id, const int* mem_fds, int mc_fd) {
+  Comm* c = (Comm*)h;
+  DriverApi* d = drv();
+  McSeg* ms = find_mc(c, seg_id);
+  B200_REQUIRE(ms != nullptr, "segment %d is not a multicast segment", seg_id);
+  Seg& s = c->segs[seg_id];
+  CUmemAllocationProp ap;
+  memset(&ap, 0, sizeof ap);
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = c->device;
+  size_t gran = 0;
+  B200_DRV(d->MemGetAllocationGranularity(&gran, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  for (int r = 0; r < c->n; ++r) {
+    if (r == c->rank) continue;
+    B200_DRV(d->MemImportFromShareableHandle(&ms->mem[r], (void*)(uintptr_t)mem_fds[r], CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+    int rc = map_rw(d, ms->mem[r], ms->size, gran, c->device, &s.base[r]);
+    if (rc) return rc;
+    close(mem_fds[r]);
+  }
+  if (c->rank != 0) {
+    B200_DRV(d->MemImportFromShareableHandle(&ms->mc, (void*)(uintptr_t)mc_fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+    close(mc_fd);
+  }
+  CUdevice cd;
+  B200_DRV(d->DeviceGet(&cd, c->device));
+  B200_DRV(d->MulticastAddDevice(ms->mc, cd));
+  return B200_OK;
+}
+
+// Step 3 (after a control-plane barrier: every rank has added its device): bind the local memory and map the
+// multicast object.
+int b200_comm_mcseg_bind(b200_comm_t h, int seg_id) {
+  Comm* c = (Comm*)h;
+  DriverApi* d = drv();
+  McSeg* ms = find_mc(c, seg_id);
+  B200_REQUIRE(ms != nullptr, "segment %d is not a multicast segment", seg_id);
+  B200_DRV(d->MulticastBindMem(ms->mc, 0, ms->mem[c->rank], 0, ms->size, 0));
+  CUmulticastObjectProp mp;
+  memset(&mp, 0, sizeof mp);
+  mp.numDevices = (unsigned)c->n;
+  mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  mp.size = ms->size;
+  size_t gran = 0;
+  B200_DRV(d->MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+  return map_rw(d, ms->mc, ms->size, gran, c->device, &ms->mc_base);
+}
+
+void* b200_comm_seg_mc_ptr(b200_comm_t h, int seg_id) {
+  McSeg* ms = find_mc((Comm*)h, seg_id);
+  return ms ? ms->mc_base : nullptr;
+}
+
+// dst = scale * sum over ranks of src, reduced in the NVSwitch. src/dst live in multicast segments.
+int b200_allreduce_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int src_seg, size_t src_off, int dst_seg,
+                        size_t dst_off, long long numel, float scale, void* stream) {
+  Comm* c = (Comm*)h;
+  McSeg *ss = find_mc(c, src_seg), *ds = find_mc(c, dst_seg);
+  B200_REQUIRE(ss && ds && ss->mc_base && ds->mc_base, "allreduce_nvls: source and destination must be bound multicast segments");
+  B200_REQUIRE(channel >= 0 && channel < MAXCH && nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  B200_REQUIRE(numel % 4 == 0, "numel %lld must be a multiple of 4", numel);
+  int rc;
+  if ((rc = check_seg(c, src_seg, src_off, numel * 4, "nvls src"))) return rc;
+  if ((rc = check_seg(c, dst_seg, dst_off, numel * 4, "nvls dst"))) return rc;
+  NvlsArgs a;
+  memset(&a, 0, sizeof a);
+  a.rank = c->rank; a.n = c->n; a.channel = channel; a.mode = 0;
+  fill_pad(c, c->rank, &a.pad);
+  a.src_mc = (const float*)((char*)ss->mc_base + src_off);
+  a.dst_mc = (float*)((char*)ds->mc_base + dst_off);
+  a.scale = scale; a.start = 0; a.numel = numel; a.timeout = c->timeout_cycles;
+  nvls_allreduce_kernel<<<nblocks, nthreads, 0, (cudaStream_t)stream>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// NVLS form of b200_fused_allreduce_adam for one range: in-switch reduction of the gradient slice, Adam on the
+// owner, multicast store of the bf16 weights. grad and w16 must live in bound multicast segments.
+int b200_fused_allreduce_adam_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int grad_seg, size_t grad_cur_off,
+                                   size_t grad_other_off, int state_seg, size_t master_off, size_t m_off, size_t v_off,
+                                   int w16_seg, size_t w16_off, int ctrl_seg, size_t step_off, size_t hyper_off, float scale,
+                                   long long start, long long numel, int zero_other, void* stream) {
+  Comm* c = (Comm*)h;
+  McSeg *gs = find_mc(c, grad_seg), *ws = find_mc(c, w16_seg);
+  B200_REQUIRE(gs && ws && gs->mc_base && ws->mc_base, "fused nvls: gradient and bf16-weight segments must be bound multicast segments");
+  B200_REQUIRE(channel >= 0 && channel < MAXCH && nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  B200_REQUIRE(start % 4 == 0 && numel % 4 == 0, "range not 4-element aligned");
+  const long long end = start + numel;
+  int rc;
+  if ((rc = check_seg(c, grad_seg, grad_cur_off, end * 4, "grad"))) return rc;
+  if ((rc = check_seg(c, grad_seg, grad_other_off, end * 4, "grad_other"))) return rc;
+  if ((rc = check_seg(c, state_seg, master_off, end * 4, "master"))) return rc;
+  if ((rc = check_seg(c, state_seg, m_off, end * 4, "adam_m"))) return rc;
+  if ((rc = check_seg(c, state_seg, v_off, end * 4, "adam_v"))) return rc;
+  if ((rc = check_seg(c, w16_seg, w16_off, end * 2, "w16"))) return rc;
+  NvlsArgs a;
+  memset(&a, 0, sizeof a);
+  a.rank = c->rank; a.n = c->n; a.channel = channel; a.mode = 1;
+  fill_pad(c, c->rank, &a.pad);
+  a.src_mc = (const float*)((char*)gs->mc_base + grad_cur_off);
+  a.w16_mc = (bf16*)((char*)ws->mc_base + w16_off);
+  a.grad_other = (float*)seg_ptr(c, grad_seg, c->rank, grad_other_off);
+  a.master = (float*)seg_ptr(c, state_seg, c->rank, master_off);
+  a.m = (float*)seg_ptr(c, state_seg, c->rank, m_off);
+  a.v = (float*)seg_ptr(c, state_seg, c->rank, v_off);
+  a.step_ptr = (const int*)seg_ptr(c, ctrl_seg, c->rank, step_off);
+  a.hyper = (const double*)seg_ptr(c, ctrl_seg, c->rank, hyper_off);
+  a.scale = scale; a.start = start; a.numel = numel; a.zero_other = zero_other; a.timeout = c->timeout_cycles;
+  nvls_allreduce_kernel<<<nblocks, nthreads, 0, (cudaStream_t)stream>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -53,6 +53,20 @@ int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads,
 /* one-sided copy of a peer's [off, off+bytes) into the same range of the local segment (rank-0 checkpoint gather,
  * horovod/tensorflow_mnist.py:157-159: only worker 0 saves) */
 int b200_comm_pull_from_peer(b200_comm_t h, int seg, size_t off, size_t bytes, int peer, void* stream);
+/* NVLS: segments bound to an NVSwitch multicast object (in-switch reduction). Three steps with the
+ * caller's control plane in between: alloc (-> POSIX fds to ship to the peers), open (import + add device),
+ * [barrier], bind.  A multicast segment is also peer-mapped, so every P2P entry point accepts it. */
+int b200_nvls_supported(void);
+int b200_comm_mcseg_alloc(b200_comm_t h, size_t bytes, int* seg_id, int* mem_fd_out, int* mc_fd_out, size_t* actual_bytes);
+int b200_comm_mcseg_open(b200_comm_t h, int seg_id, const int* mem_fds, int mc_fd);
+int b200_comm_mcseg_bind(b200_comm_t h, int seg_id);
+void* b200_comm_seg_mc_ptr(b200_comm_t h, int seg_id);
+int b200_allreduce_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int src_seg, size_t src_off, int dst_seg,
+                        size_t dst_off, long long numel, float scale, void* stream);
+int b200_fused_allreduce_adam_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int grad_seg, size_t grad_cur_off,
+                                   size_t grad_other_off, int state_seg, size_t master_off, size_t m_off, size_t v_off,
+                                   int w16_seg, size_t w16_off, int ctrl_seg, size_t step_off, size_t hyper_off, float scale,
+                                   long long start, long long numel, int zero_other, void* stream);
 /* hvd.Adasum (horovod/tensorflow_mnist.py:133), one tree level per call */
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg);
 int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cur_seg, size_t cur_off, int next_seg,

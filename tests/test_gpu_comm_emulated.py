@@ -150,6 +150,27 @@ def test_plain_allreduce_broadcast(n, algo):
         a.close()
 
 
+@pytest.mark.parametrize("n,root", [(4, 1), (8, 0), (8, 5)])
+def test_large_broadcast_scatter_allgather(n, root):
+    """>= 1 MB and more than two ranks takes the two-phase path (scatter from the root, all-gather between ranks)."""
+    N = 300_000 + 4 * n
+    a = SymmetricArena.emulated(n)
+    a.set_timeout_ms(2000)
+    try:
+        seg = a.alloc(N * 4 * 2)
+        for r in range(n):
+            a.view(seg, 0, N, torch.float32, r).copy_(torch.arange(N, device="cuda", dtype=torch.float32) * (r + 1))
+            a.view(seg, N * 4, N, torch.float32, r).fill_(-1.0)
+        for _ in range(2):
+            K.check(K.lib().b200_broadcast(a.h, 3, 8, 256, root, seg, 0, seg, N * 4, N, _stream()))
+        torch.cuda.synchronize()
+        want = torch.arange(N, device="cuda", dtype=torch.float32) * (root + 1)
+        for r in range(n):
+            assert torch.equal(a.view(seg, N * 4, N, torch.float32, r), want), f"rank {r}"
+    finally:
+        a.close()
+
+
 @pytest.mark.parametrize("n", [2, 4, 8])
 def test_adasum_levels_match_tree(n):
     torch.manual_seed(n + 100)

@@ -40,10 +40,12 @@ def _check(res, np_, algo):
         assert r0["oracle_cos"] > 0.9 and r0["adam_m_cos"] > 0.95, r0
     if algo == "twoshot":
         assert r0["sharded_ranges"] >= 1
+    if algo == "nvls" and r0.get("nvls_supported"):
+        assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
 
 
 @pytest.mark.multigpu(2)
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum", "nvls"])
 def test_two_gpus(tmp_path, algo):
     _check(_run(2, algo, tmp_path), 2, algo)
 
@@ -55,6 +57,6 @@ def test_four_gpus(tmp_path, algo):
 
 
 @pytest.mark.multigpu(8)
-@pytest.mark.parametrize("algo", ["auto", "twoshot", "adasum"])
+@pytest.mark.parametrize("algo", ["auto", "twoshot", "adasum", "nvls"])
 def test_eight_gpus(tmp_path, algo):
     _check(_run(8, algo, tmp_path), 8, algo)

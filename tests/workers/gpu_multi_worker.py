@@ -47,6 +47,10 @@ res["int_sum"] = int(ints[0])
 B = 32
 spec = hvd.get_spec("mnist_cnn")
 use_adasum = algo == "adasum"
+if algo == "nvls":
+    res["nvls_supported"] = bool(hvd.world().arena.nvls_supported())
+    if not res["nvls_supported"]:
+        algo = "twoshot"
 opt = hvd.DistributedOptimizer(hvd.Adam(1e-3 * (1 if use_adasum else n)), op=hvd.Adasum if use_adasum else hvd.Average,
                                algo="auto" if use_adasum else algo)
 eng = hvd.make_engine(spec, opt, engine="b200", batch_size=B, seed=11 + r, dropout=False)   # different init per rank on purpose
@@ -63,6 +67,8 @@ digest = hashlib.sha256(eng.w16.cpu().view(torch.int16).numpy().tobytes()).hexdi
 digests = hvd.allgather_object(digest)
 res["replicas_bitwise_identical"] = len(set(digests)) == 1
 res["sharded_ranges"] = len(eng._sharded_ranges)
+res["engine_nvls"] = bool(eng.nvls)
+res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
 # rank 0 alone takes a checkpoint (one-sided gather of sharded Adam state) while the others wait at a barrier
 if r == 0:
