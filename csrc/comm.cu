@@ -1021,18 +1021,31 @@ __global__ void __launch_bounds__(512) nvls_allreduce_kernel(const NvlsArgs a) {
   long long chunk = (a.numel + a.n - 1) / a.n;
   chunk = (chunk + 3) / 4 * 4;
   const long long lo = min((long long)a.rank * chunk, a.numel), hi = min(lo + chunk, a.numel);
-  for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
-    const long long i = a.start + lo + q * 4;
-    float4 g = multimem_ld_reduce_f4(a.src_mc + i);
-    g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
-    if (a.mode == 0) {
-      multimem_st_f4(a.dst_mc + i, g);
-    } else {
-      float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
-      adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
-      adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
-      st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
-      multimem_st_b64(a.w16_mc + i, pack_bf16x4(p));
+  // four in-switch reductions in flight per thread: the round trip through the NVSwitch is several microseconds
+  const long long nq = (hi - lo) / 4;
+  for (long long q0 = tid; q0 < nq; q0 += 4 * nthr) {
+    float4 g[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long q = q0 + u * nthr;
+      if (q < nq) g[u] = multimem_ld_reduce_f4(a.src_mc + a.start + lo + q * 4);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long q = q0 + u * nthr;
+      if (q >= nq) continue;
+      const long long i = a.start + lo + q * 4;
+      float4 gg = g[u];
+      gg.x *= a.scale; gg.y *= a.scale; gg.z *= a.scale; gg.w *= a.scale;
+      if (a.mode == 0) {
+        multimem_st_f4(a.dst_mc + i, gg);
+      } else {
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        adam_elem(gg.x, p.x, m.x, v.x, c); adam_elem(gg.y, p.y, m.y, v.y, c);
+        adam_elem(gg.z, p.z, m.z, v.z, c); adam_elem(gg.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        multimem_st_b64(a.w16_mc + i, pack_bf16x4(p));
+      }
     }
   }
   if (a.mode == 1 && a.zero_other)

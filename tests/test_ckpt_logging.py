@@ -107,3 +107,33 @@ def test_data_pipeline(tmp_path):
     assert all(b[0].shape == (64, 784) and b[1].shape == (64,) for b in seen)
     first_epoch = np.concatenate([b[1] for b in seen[:4]])               # 300//64 = 4 full batches, tail dropped
     assert len(first_epoch) == 256
+
+
+def test_stall_watchdog_warns_and_recovers(capsys):
+    import time
+    from b200dp.utils.watchdog import StallWatchdog
+    wd = StallWatchdog(warn_secs=0.2, poll_secs=0.05).start()
+    wd.beat(7)
+    time.sleep(0.55)
+    assert wd.warnings >= 2
+    before = wd.warnings
+    for _ in range(6):
+        wd.beat(8)
+        time.sleep(0.05)
+    assert wd.warnings == before                     # beating keeps it quiet
+    wd.stop()
+    out = capsys.readouterr().out
+    assert '"event":"stall"' in out and '"step":7' in out
+
+
+def test_topology_discovery_on_cpu():
+    from b200dp.runtime import topology
+    t = topology.discover()
+    assert "numa" in t and t["host_cpus"] >= 1 and isinstance(t["gpus"], list)
+
+
+def test_keras128_falls_back_to_torch_engine():
+    import b200dp as hvd
+    eng = hvd.make_engine(hvd.get_spec("keras128", 0.25), hvd.Adam(1e-3), engine="torch")
+    r = eng.train_step(np.random.rand(4, 784).astype(np.float32), np.array([1, 2, 3, 4]))
+    assert np.isfinite(r.loss_value())
