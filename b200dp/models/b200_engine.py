@@ -198,6 +198,8 @@ class B200Engine(Engine):
             return (b.start, b.numel, algo, 1)
         by = {b.name: b for b in buckets}
         self.comm_dense = [rng(by["dense.kernel"])]
+        # dense.kernel's gradient is produced by plain stores (GEMM epilogue), never accumulated: nothing to clear
+        self.comm_dense = [(r[0], r[1], r[2], 0) for r in self.comm_dense]
         self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1.+conv2."])]
         self.adasum = adasum
         self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0

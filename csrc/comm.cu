@@ -119,17 +119,25 @@ __device__ __forceinline__ float adam_elem(float g, float& p, float& m, float& v
   return p;
 }
 
-// All peer loads are issued before the first add (8 independent 16-byte NVLink reads in flight per thread);
-// the sum itself runs in fixed rank order so every rank computes the same bits.
+// Peer loads are issued four at a time before their adds (4 independent 16-byte NVLink reads in flight per thread
+// without blowing the register budget); the sum runs in fixed rank order so every rank computes the same bits.
 __device__ __forceinline__ float4 reduce_ptrs(const float* const* ptrs, int n, long long i) {
-  float4 t[MAXR];
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-  for (int r = 0; r < MAXR; ++r)
-    if (r < n) t[r] = ld_f4(ptrs[r] + i);
-  float4 s = t[0];
+  for (int r0 = 0; r0 < MAXR; r0 += 4) {
+    if (r0 < n) {
+      float4 t[4];
 #pragma unroll
-  for (int r = 1; r < MAXR; ++r)
-    if (r < n) { s.x += t[r].x; s.y += t[r].y; s.z += t[r].z; s.w += t[r].w; }
+      for (int k = 0; k < 4; ++k)
+        if (r0 + k < n) t[k] = ld_f4(ptrs[r0 + k] + i);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (r0 + k < n) {
+          if (r0 + k == 0) s = t[k];
+          else { s.x += t[k].x; s.y += t[k].y; s.z += t[k].z; s.w += t[k].w; }
+        }
+    }
+  }
   return s;
 }
 
@@ -140,7 +148,7 @@ __device__ __forceinline__ float4 reduce_peers(const FusedArgs& a, long long i) 
 }
 
 template <bool EMU>
-__global__ void __launch_bounds__(512) fused_allreduce_adam_kernel(const FusedArgs areal, const FusedArgs* aemu) {
+__global__ void __launch_bounds__(512, 2) fused_allreduce_adam_kernel(const FusedArgs areal, const FusedArgs* aemu) {
   const FusedArgs& a = EMU ? aemu[blockIdx.y] : areal;
   const int bid = blockIdx.x;
   const long long tid = (long long)bid * blockDim.x + threadIdx.x;
@@ -172,28 +180,18 @@ __global__ void __launch_bounds__(512) fused_allreduce_adam_kernel(const FusedAr
   for (int ri = 0; ri < a.nranges; ++ri) {
     const Range rg = a.ranges[ri];
     if (rg.algo == 0 || !multi) {
-      // one-shot: every rank reduces and updates the whole range (two vectors in flight per thread)
+      // one-shot: every rank reduces and updates the whole range; all loads of an element (N peer gradients,
+      // master, m, v) are issued before the first use
       const long long nq = rg.numel / 4;
-      for (long long q = tid; q < nq; q += 2 * nthr) {
-        const long long i0 = rg.start + q * 4;
-        const bool two = q + nthr < nq;
-        const long long i1 = two ? i0 + nthr * 4 : i0;
-        const float4 g0 = reduce_peers(a, i0);
-        const float4 g1 = two ? reduce_peers(a, i1) : g0;
-        float4 p0 = ld_f4(a.master + i0), m0 = ld_f4(a.m + i0), v0 = ld_f4(a.v + i0);
-        float4 p1 = ld_f4(a.master + i1), m1 = ld_f4(a.m + i1), v1 = ld_f4(a.v + i1);
-        adam_elem(g0.x, p0.x, m0.x, v0.x, c); adam_elem(g0.y, p0.y, m0.y, v0.y, c);
-        adam_elem(g0.z, p0.z, m0.z, v0.z, c); adam_elem(g0.w, p0.w, m0.w, v0.w, c);
-        st_f4(a.master + i0, p0); st_f4(a.m + i0, m0); st_f4(a.v + i0, v0);
-        *reinterpret_cast<uint2*>(a.w16[a.rank] + i0) = pack_bf16x4(p0);
-        if (rg.zero_other) st_f4(a.grad_other + i0, make_float4(0.f, 0.f, 0.f, 0.f));
-        if (two) {
-          adam_elem(g1.x, p1.x, m1.x, v1.x, c); adam_elem(g1.y, p1.y, m1.y, v1.y, c);
-          adam_elem(g1.z, p1.z, m1.z, v1.z, c); adam_elem(g1.w, p1.w, m1.w, v1.w, c);
-          st_f4(a.master + i1, p1); st_f4(a.m + i1, m1); st_f4(a.v + i1, v1);
-          *reinterpret_cast<uint2*>(a.w16[a.rank] + i1) = pack_bf16x4(p1);
-          if (rg.zero_other) st_f4(a.grad_other + i1, make_float4(0.f, 0.f, 0.f, 0.f));
-        }
+      for (long long q = tid; q < nq; q += nthr) {
+        const long long i = rg.start + q * 4;
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        const float4 g = reduce_peers(a, i);
+        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        *reinterpret_cast<uint2*>(a.w16[a.rank] + i) = pack_bf16x4(p);
+        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(0.f, 0.f, 0.f, 0.f));
       }
     } else {
       // two-shot: reduce + update the owned slice, push the bf16 result to every rank

@@ -5,13 +5,13 @@
 // second convolution: 25 taps x 32 x 64 bf16 = 100 KB) this kernel instead
 //   * loads the filter bank ONCE per CTA (TMA, 128B-swizzled tiles, one mbarrier per tap so the first MMAs can
 //     start after 4 KB), and keeps it for every image the CTA processes (persistent loop, grid = min(#SM, B));
-//   * loads each image ONCE, halo included, with a single 5-D TMA box into the UMMA *no-swizzle* canonical
+//   * loads each image ONCE (two loader warps, coalesced 16-byte loads) into the UMMA *no-swizzle* canonical
 //     layout [channel-chunk of 8][pixel row-major, 16 wide][8 channels]: consecutive pixels of a chunk are 16 B
 //     apart, so an 8-pixel core matrix is 128 contiguous bytes (SBO = 128 B) and the two 8-channel chunks of a
 //     K=16 step are a chunk stride apart (LBO).  In that layout a filter tap is nothing but a different
 //     16-byte-aligned START ADDRESS in the A descriptor: tap (kh,kw) starts (kh*16 + kw - pad) pixels later.
-//     The zero halo comes from TMA out-of-bounds fill: columns W..15 of each 16-wide row double as the right
-//     padding of that row and the left padding of the next.
+//     The halo is zeroed once per CTA and never written again: columns W..15 of each 16-wide row double as the
+//     right padding of that row and the left padding of the next.
 // Accumulators are double-buffered in TMEM (image parity x 2 row-tiles) so the pooling epilogue of one tile
 // overlaps the MMAs of the next.  Same math and same epilogue as conv_tc.cu.
 //
@@ -37,6 +37,7 @@ struct HaloParams {
   int img_bytes;       // (Cred/8) * chunk_bytes
   int wtile_bytes;     // one tap's weight tile
   int relu, pool;
+  const bf16* act;     // input activation [B,H,W,Cred]
   const bf16* bias;
   bf16* out;
   uint8_t* argmax;
@@ -44,7 +45,7 @@ struct HaloParams {
   int dbg;             // experiment switches: 1 skip MMAs, 2 skip image loads, 4 skip weight loads
 };
 
-__device__ __forceinline__ void halo_epilogue(const HaloParams& p, uint32_t taddr, int img, int h0, int lane, int q) {
+__device__ __forceinline__ void halo_epilogue(const HaloParams& p, const float* sbias, uint32_t taddr, int img, int h0, int lane, int q) {
   const int hh = 2 * q + (lane >> 4), ww = lane & 15;
   const int h = h0 + hh;
   for (int c = 0; c < p.N; c += 16) {
@@ -55,7 +56,7 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, uint32_t tadd
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
       v[j] = __uint_as_float(r[j]);
-      if (p.bias) v[j] += __bfloat162float(p.bias[c + j]);
+      v[j] += sbias[c + j];
       if (p.relu) v[j] = fmaxf(v[j], 0.f);
     }
     if (p.pool) {
@@ -100,8 +101,7 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* m, uin
 }
 
 template <int KK, int KSTEPS, int MODE>
-__global__ void __launch_bounds__(192, 1) conv_halo_kernel(const __grid_constant__ CUtensorMap tmImg,
-                                                           const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
+__global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   constexpr int ntaps = KK * KK;
@@ -114,23 +114,25 @@ __global__ void __launch_bounds__(192, 1) conv_halo_kernel(const __grid_constant
   uint64_t* tfull = aempty + 2;
   uint64_t* tempty = tfull + 4;
   uint32_t* tmem_slot = (uint32_t*)(tempty + 4);
+  float* sbias = (float*)(tmem_slot + 4);                      // p.N floats (zeros when the conv has no bias)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nimg = (p.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;    // images this CTA handles
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmImg);
     tma_prefetch_desc(&tmW);
     for (int t = 0; t < ntaps; ++t) mbar_init(wfull + t, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(afull + i, 1); mbar_init(aempty + i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(afull + i, 128); mbar_init(aempty + i, 1); }
     for (int i = 0; i < 4; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
     fence_barrier_init();
   }
-  // zero the guard bytes around the image buffers (read by the taps that reach before/after a buffer)
-  for (int i = threadIdx.x; i < 3 * 32; i += blockDim.x) {
-    const int which = i / 32, word = i % 32;
-    uint8_t* g = which == 0 ? sImg0 - 128 : (which == 1 ? sImg0 + p.img_bytes : sImg0 + img_stride + p.img_bytes);
-    reinterpret_cast<uint32_t*>(g)[word] = 0u;
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+  // Zero both image buffers and their guard bytes once: the loader warps only ever write real pixels, so the halo
+  // (rows -pad..-1 and H.., columns W..15) and the guards stay zero for every image this CTA processes.
+  {
+    uint4* z = reinterpret_cast<uint4*>(sImg0 - 128);
+    const int n16 = (2 * img_stride + 128) / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
   }
   fence_proxy_async();
   if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -150,20 +152,6 @@ __global__ void __launch_bounds__(192, 1) conv_halo_kernel(const __grid_constant
       }
     }
     __syncwarp();
-    for (int it = 0; it < nimg; ++it) {
-      const int buf = it & 1;
-      const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-      mbar_wait(aempty + buf, ph ^ 1u, 31);
-      if (leader) {
-        if (p.dbg & 2) {
-          mbar_arrive(afull + buf);
-        } else {
-          mbar_arrive_expect_tx(afull + buf, (uint32_t)p.img_bytes);
-          tma_load_5d(sImg0 + buf * img_stride, &tmImg, afull + buf, 0, 0, -p.pad, 0, blockIdx.x + it * gridDim.x);
-        }
-      }
-      __syncwarp();
-    }
   } else if (warp == 1) {
     // Uniform loops, fully unrolled over taps and K steps; one elected lane issues.  An A descriptor is a constant
     // high word plus (image base + tap pixel offset + chunk offset) in the 14-bit start-address field.
@@ -204,6 +192,42 @@ __global__ void __launch_bounds__(192, 1) conv_halo_kernel(const __grid_constant
       if (leader) umma_commit(aempty + buf);          // both tiles' MMAs have consumed the image buffer
       __syncwarp();
     }
+  } else if (warp >= 6) {
+    // ===== image loaders (4 warps): coalesced 16-byte global loads, scattered into the chunked no-swizzle layout
+    // [channel chunk][row][16 px][8 ch].  (A 5-D TMA box can produce this layout too, but with a 16-byte inner
+    // dimension it issues one request per pixel-chunk and was the bottleneck of the kernel.)
+    const int lt = threadIdx.x - 192;
+    const int CK = p.Cred / 8;
+    const int pieces = p.H * p.W * CK;
+    constexpr int UNR = 13;              // 128 threads x 13 x 16 B covers the 25 KB dgrad image in one round trip
+    for (int it = 0; it < nimg; ++it) {
+      const int buf = it & 1;
+      mbar_wait(aempty + buf, (((uint32_t)(it >> 1)) & 1u) ^ 1u, 31);
+      const int img = blockIdx.x + it * gridDim.x;
+      const uint4* src = reinterpret_cast<const uint4*>(p.act + (size_t)img * p.H * p.W * p.Cred);
+      uint8_t* dst = sImg0 + buf * img_stride;
+      if (!(p.dbg & 2)) {
+        for (int base = 0; base < pieces; base += 128 * UNR) {
+          uint4 v[UNR];
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) {
+            const int idx = base + u * 128 + lt;
+            if (idx < pieces) v[u] = __ldg(src + idx);
+          }
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) {
+            const int idx = base + u * 128 + lt;
+            if (idx < pieces) {
+              const int pixel = idx / CK, chunk = idx - pixel * CK;
+              const int h = pixel / p.W, w = pixel - h * p.W;
+              *reinterpret_cast<uint4*>(dst + chunk * p.chunk_bytes + ((h + p.pad) * ROWPIX + w) * 16) = v[u];
+            }
+          }
+        }
+      }
+      fence_proxy_async();                 // generic-proxy stores -> visible to the tensor core's async proxy
+      mbar_arrive(afull + buf);
+    }
   } else {
     const int q = warp & 3;
     for (int it = 0; it < nimg; ++it) {
@@ -212,7 +236,7 @@ __global__ void __launch_bounds__(192, 1) conv_halo_kernel(const __grid_constant
         const int acc = (it & 1) * 2 + tile;
         mbar_wait(tfull + acc, (uint32_t)(it >> 1) & 1u, 35);
         tc_fence_after();
-        halo_epilogue(p, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.N), img, tile * 8, lane, q);
+        if (!(p.dbg & 8)) halo_epilogue(p, sbias, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.N), img, tile * 8, lane, q);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty + acc);
@@ -251,25 +275,19 @@ int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* 
   if (cols > 512) return B200_ERR_UNSUPPORTED;
   p.tmem_cols = cols;
   { const char* e = getenv("B200DP_HALO_DBG"); p.dbg = e ? atoi(e) : 0; }
-  const size_t smem = 1024 + (size_t)wbytes + 128 + 2 * ((size_t)p.img_bytes + 128) + (ntaps + 12) * 8 + 64;
+  const size_t smem = 1024 + (size_t)wbytes + 128 + 2 * ((size_t)p.img_bytes + 128) + (ntaps + 12) * 8 + 64 + (size_t)N * 4;
   if (smem > 220 * 1024) return B200_ERR_UNSUPPORTED;
 
-  CUtensorMap tmImg, tmW;
+  CUtensorMap tmW;
   int rc;
-  {
-    // activation [B,H,W,C] viewed as 5-D {8 ch, W, H, C/8 chunks, B}: the box lands as [chunk][row][16 px][8 ch]
-    const uint64_t dims[5] = {8, (uint64_t)W, (uint64_t)H, (uint64_t)Cred / 8, (uint64_t)B};
-    const uint64_t str[4] = {(uint64_t)Cred * 2, (uint64_t)W * Cred * 2, 16, (uint64_t)H * W * Cred * 2};
-    const uint32_t box[5] = {8, ROWPIX, (uint32_t)p.rows, (uint32_t)Cred / 8, 1};
-    if ((rc = tc::make_tmap_bf16(&tmImg, act, 5, dims, str, box, 0))) return rc;
-  }
+  p.act = (const bf16*)act;
   {
     const uint64_t dims[2] = {(uint64_t)Co, (uint64_t)ntaps * Ci}, str[1] = {(uint64_t)Co * 2};
     const uint32_t box[2] = {(uint32_t)Co, (uint32_t)Ci};
     if ((rc = tc::make_tmap_bf16(&tmW, w, 2, dims, str, box, 128))) return rc;
   }
   const int ksteps = Cred / 16;
-  void (*kern)(const CUtensorMap, const CUtensorMap, const HaloParams) = nullptr;
+  void (*kern)(const CUtensorMap, const HaloParams) = nullptr;
   if (k == 5 && mode == 0 && ksteps == 2) kern = conv_halo_kernel<5, 2, 0>;
   else if (k == 5 && mode == 1 && ksteps == 4) kern = conv_halo_kernel<5, 4, 1>;
   else if (k == 3 && mode == 0 && ksteps == 2) kern = conv_halo_kernel<3, 2, 0>;
@@ -284,7 +302,7 @@ int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* 
       if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = B < 148 ? B : 148;
-  kern<<<grid, 192, smem, st>>>(tmImg, tmW, p);
+  kern<<<grid, 320, smem, st>>>(tmW, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -55,7 +55,7 @@ namespace {
 
 using namespace tc;
 
-constexpr int BM = 128, BK = 64, NSTAGE = 4;
+constexpr int BM = 128, BK = 64, MAX_STAGE = 4;
 constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
 
 struct GemmParams {
@@ -64,6 +64,7 @@ struct GemmParams {
   int a_mn, b_mn, out_mode, bn;
   int kb_total, kb_per_split;
   uint32_t tmem_cols;
+  int nstage;          // pipeline depth: min(4, k-blocks per CTA) — a short K keeps shared memory small (more CTAs per SM)
 };
 
 __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -71,6 +72,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int stage_bytes = A_TILE_BYTES + p.bn * BK * 2;
+  const int NSTAGE = p.nstage;
   uint64_t* full = (uint64_t*)(smem + NSTAGE * stage_bytes);
   uint64_t* empty = full + NSTAGE;
   uint64_t* tmem_full = empty + NSTAGE;
@@ -148,49 +150,54 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
       if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> global =====
+    // ===== epilogue: TMEM -> registers -> global (thread = one output row, 16 columns per step) =====
     mbar_wait(tmem_full, 0, 3);
     tc_fence_after();
     const int q = warp & 3;                         // TMEM lane quarter this warp may touch
     const int row = m0 + q * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    for (int c = 0; c < p.bn; c += 16) {
-      uint32_t r[16];
-      tmem_ld_32x16(taddr + c, r);
-      tmem_ld_wait();
-      if (row < p.M) {
-        const int col = n0 + c;
-        if (p.out_mode == 1) {
-          bf16* dst = (bf16*)p.C + (size_t)row * p.ldc + col;
-          if (col + 16 <= p.N) {
-            uint4 lo, hi;
-            uint2 t;
-            t = pack_bf16x4(make_float4(__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])));
-            lo.x = t.x; lo.y = t.y;
-            t = pack_bf16x4(make_float4(__uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7])));
-            lo.z = t.x; lo.w = t.y;
-            t = pack_bf16x4(make_float4(__uint_as_float(r[8]), __uint_as_float(r[9]), __uint_as_float(r[10]), __uint_as_float(r[11])));
-            hi.x = t.x; hi.y = t.y;
-            t = pack_bf16x4(make_float4(__uint_as_float(r[12]), __uint_as_float(r[13]), __uint_as_float(r[14]), __uint_as_float(r[15])));
-            hi.z = t.x; hi.w = t.y;
-            *reinterpret_cast<uint4*>(dst) = lo;
-            *reinterpret_cast<uint4*>(dst + 8) = hi;
+    const int out_mode = p.out_mode, N = p.N, bn = p.bn;
+    const bool row_ok = row < p.M;
+    bf16* const c16 = (bf16*)p.C + (size_t)row * p.ldc;
+    float* const c32 = (float*)p.C + (size_t)row * p.ldc;
+    uint32_t r[2][16];
+    tmem_ld_32x16(taddr, r[0]);
+#pragma unroll 1
+    for (int c = 0; c < bn; c += 32) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int cc = c + half * 16;
+        if (cc >= bn) break;
+        tmem_ld_wait();                                              // r[half] is ready
+        if (cc + 16 < bn) tmem_ld_32x16(taddr + cc + 16, r[half ^ 1]);  // next chunk in flight while this one is stored
+        if (!row_ok) continue;
+        const int col = n0 + cc;
+        const int valid = N - col;
+        const uint32_t* v = r[half];
+        if (valid >= 16) {
+          if (out_mode == 1) {
+            uint2 t0 = pack_bf16x4(make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])));
+            uint2 t1 = pack_bf16x4(make_float4(__uint_as_float(v[4]), __uint_as_float(v[5]), __uint_as_float(v[6]), __uint_as_float(v[7])));
+            uint2 t2 = pack_bf16x4(make_float4(__uint_as_float(v[8]), __uint_as_float(v[9]), __uint_as_float(v[10]), __uint_as_float(v[11])));
+            uint2 t3 = pack_bf16x4(make_float4(__uint_as_float(v[12]), __uint_as_float(v[13]), __uint_as_float(v[14]), __uint_as_float(v[15])));
+            *reinterpret_cast<uint4*>(c16 + col) = make_uint4(t0.x, t0.y, t1.x, t1.y);
+            *reinterpret_cast<uint4*>(c16 + col + 8) = make_uint4(t2.x, t2.y, t3.x, t3.y);
           } else {
-            for (int j = 0; j < 16 && col + j < p.N; ++j) dst[j] = __float2bfloat16(__uint_as_float(r[j]));
-          }
-        } else {
-          float* dst = (float*)p.C + (size_t)row * p.ldc + col;
-          if (col + 16 <= p.N) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
-              const float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-              if (p.out_mode == 2) red_add_f4(dst + j, v);
-              else st_f4(dst + j, v);
+              const float4 f = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              if (out_mode == 2) red_add_f4(c32 + col + j, f);
+              else st_f4(c32 + col + j, f);
             }
-          } else {
-            for (int j = 0; j < 16 && col + j < p.N; ++j) {
-              if (p.out_mode == 2) atomicAdd(dst + j, __uint_as_float(r[j]));
-              else dst[j] = __uint_as_float(r[j]);
+          }
+        } else if (valid > 0) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (j < valid) {
+              const float f = __uint_as_float(v[j]);
+              if (out_mode == 1) c16[col + j] = __float2bfloat16(f);
+              else if (out_mode == 2) atomicAdd(c32 + col + j, f);
+              else c32[col + j] = f;
             }
           }
         }
@@ -245,7 +252,9 @@ extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N,
   uint32_t cols = 32;
   while ((int)cols < block_n) cols <<= 1;
   p.tmem_cols = cols;
-  const size_t smem = (size_t)NSTAGE * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
+  p.nstage = p.kb_per_split < MAX_STAGE ? p.kb_per_split : MAX_STAGE;
+  if (p.nstage < 2) p.nstage = 2;
+  const size_t smem = (size_t)p.nstage * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
   static size_t smem_set = 0;
   if (smem > smem_set) {
     B200_CHECK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -39,16 +39,21 @@ __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __rest
     const float bb = c < C1 ? bf(bias + c) : 0.f;
     for (int p = blockIdx.y * 49 + warp; p < (blockIdx.y + 1) * 49; p += nwarp) {
       const int ph = p / 14, pw = p % 14;
+      // the four conv outputs under one pooling window share a 6x6 input patch: read it once into registers
+      float win[6][6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 6; ++cc) win[r][cc] = img[2 * ph + r][2 * pw + cc];
       float best = -1.f;
       int bi = 0;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const int y = 2 * ph + (q >> 1), xq = 2 * pw + (q & 1);
         float acc = bb;
 #pragma unroll
         for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
-          for (int kw = 0; kw < 5; ++kw) acc = fmaf(img[y + kh][xq + kw], wr[kh * 5 + kw], acc);
+          for (int kw = 0; kw < 5; ++kw) acc = fmaf(win[(q >> 1) + kh][(q & 1) + kw], wr[kh * 5 + kw], acc);
         acc = fmaxf(acc, 0.f);
         if (acc > best) { best = acc; bi = q; }
       }
@@ -84,10 +89,25 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
       }
       __syncthreads();
       if (c < C1) {
-        for (int p = blockIdx.y * 49 + warp; p < (blockIdx.y + 1) * 49; p += nwarp) {
-          const size_t o = ((size_t)b * 196 + p) * C1 + c;
-          const float g = bf(a1 + o) > 0.f ? bf(da1 + o) : 0.f;
-          const int q = argmax[o];
+        // all global loads of this warp's (at most 7) pixels are issued before the first FMA
+        float gv[7];
+        int qv[7];
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const int p = blockIdx.y * 49 + warp + i * 8;
+          gv[i] = 0.f; qv[i] = 0;
+          if (warp + i * 8 < 49) {
+            const size_t o = ((size_t)b * 196 + p) * C1 + c;
+            gv[i] = bf(a1 + o) > 0.f ? bf(da1 + o) : 0.f;
+            qv[i] = argmax[o];
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          if (warp + i * 8 >= 49) continue;
+          const int p = blockIdx.y * 49 + warp + i * 8;
+          const float g = gv[i];
+          const int q = qv[i];
           const int y = 2 * (p / 14) + (q >> 1), xq = 2 * (p % 14) + (q & 1);
 #pragma unroll
           for (int kh = 0; kh < 5; ++kh)
@@ -126,12 +146,24 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
                                                            float* __restrict__ logits_out, float* __restrict__ loss_sum,
                                                            int* __restrict__ correct, int B, int D, int NC, float drop_rate,
                                                            int training, uint64_t seed, const int* step_ptr, int layer_id,
-                                                           int zero_z, int ring) {
-  extern __shared__ float hs[];            // D floats: bf16-rounded h
+                                                           int zero_z, int ring, int stage_w2) {
+  extern __shared__ float hs[];            // D floats: bf16-rounded h, then (optionally) a copy of W2
   __shared__ float part[8][NC_MAX];
   __shared__ float dl[NC_MAX];
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  // W2 ([D,NC] bf16, 20 KB for the MNIST head) is read twice per row with a stride the coalescer dislikes:
+  // stage it once per block with 16-byte loads and serve both passes from shared memory.
+  const bf16* w2p = w2;
+  if (stage_w2) {
+    bf16* w2s = reinterpret_cast<bf16*>(hs + D);
+    const int n16 = D * NC * 2 / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(w2);
+    uint4* dst = reinterpret_cast<uint4*>(w2s);
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = __ldg(src + i);
+    w2p = w2s;
+    __syncthreads();
+  }
   const bool drop = training && drop_rate > 0.f;
   const uint32_t step = step_ptr ? (uint32_t)*step_ptr : 0u;
   const uint32_t thresh = (uint32_t)fminf(drop_rate * 4294967296.f, 4294967295.f);
@@ -159,7 +191,7 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
       if (hv != 0.f) {
 #pragma unroll
         for (int k = 0; k < NC_MAX; ++k)
-          if (k < NC) acc[k] = fmaf(hv, bf(w2 + (size_t)j * NC + k), acc[k]);
+          if (k < NC) acc[k] = fmaf(hv, bf(w2p + (size_t)j * NC + k), acc[k]);
       }
     }
   }
@@ -203,7 +235,7 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
     if (hs[j] > 0.f) {
 #pragma unroll
       for (int k = 0; k < NC_MAX; ++k)
-        if (k < NC) g = fmaf(dlr[k], bf(w2 + (size_t)j * NC + k), g);
+        if (k < NC) g = fmaf(dlr[k], bf(w2p + (size_t)j * NC + k), g);
       g *= keep_scale;
     }
     dz_out[(size_t)b * D + j] = __float2bfloat16(g);
@@ -510,7 +542,7 @@ int b200_conv1_pool_fwd(const float* x, const void* w, const void* bias, void* o
 int b200_conv1_wgrad(const float* x, const void* da1, const void* a1, const uint8_t* argmax, float* dw, float* dbias,
                      int B, int C1, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1 wgrad: bad shape");
-  const int grid = B < 148 ? B : 148;
+  const int grid = B < 74 ? B : 74;          // several images per block: one atomic flush per block, not per image
   conv1_wgrad_kernel<<<dim3(grid, 4), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)da1, (const bf16*)a1, argmax, dw, dbias, B, C1);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -523,7 +555,9 @@ int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, 
   B200_REQUIRE(NC >= 1 && NC <= 16, "head: NC=%d outside [1,16]", NC);
   B200_REQUIRE(D % 4 == 0 && D > 0 && (size_t)D * 4 <= 200 * 1024, "head: D=%d must be a multiple of 4 and fit shared memory", D);
   B200_REQUIRE(drop_rate >= 0.f && drop_rate < 1.f, "head: drop_rate %f", drop_rate);
-  const size_t smem = (size_t)D * sizeof(float);
+  const size_t w2_bytes = (size_t)D * NC * 2;
+  const int stage_w2 = (w2_bytes % 16 == 0 && ((uintptr_t)w2 & 15) == 0 && w2_bytes <= 64 * 1024) ? 1 : 0;
+  const size_t smem = (size_t)D * sizeof(float) + (stage_w2 ? w2_bytes : 0);
   static bool attr_set = false;
   if (!attr_set) {
     B200_CHECK(cudaFuncSetAttribute(head_fwd_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -531,7 +565,7 @@ int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, 
   }
   head_fwd_bwd_kernel<16><<<B, 256, smem, (cudaStream_t)stream>>>(z, (const bf16*)b1, (const bf16*)w2, (const bf16*)b2, labels,
                                                                  (bf16*)h, (bf16*)dz, dlogits, logits_out, loss_sum, correct, B,
-                                                                 D, NC, drop_rate, training, seed, step_ptr, layer_id, zero_z, ring);
+                                                                 D, NC, drop_rate, training, seed, step_ptr, layer_id, zero_z, ring, stage_w2);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
