@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #define B200_OK 0
 #define B200_ERR_CUDA 1
@@ -33,6 +34,35 @@ void b200_set_error(const char* fmt, ...);
 #define B200_LAUNCH_CHECK() B200_CHECK(cudaGetLastError())
 
 typedef __nv_bfloat16 bf16;
+
+// ----------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL): a kernel launched with launch_pdl() may start while its predecessor in
+// the stream is still running; everything before pdl_wait() (shared-memory carve-up, barrier init, TMEM
+// allocation, descriptor prefetch) overlaps the predecessor's tail, and pdl_wait() returns once the
+// predecessor has completed and its writes are visible.  Both calls are no-ops for ordinary launches.
+// ----------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
+int b200_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = b200_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 

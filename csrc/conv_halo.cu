@@ -126,7 +126,6 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
     for (int i = 0; i < 4; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
   // Zero both image buffers and their guard bytes once: the loader warps only ever write real pixels, so the halo
   // (rows -pad..-1 and H.., columns W..15) and the guards stay zero for every image this CTA processes.
   {
@@ -140,6 +139,11 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
+  pdl_launch_dependents();
+  // the bias is a weight written by the optimizer kernel: read it only after the dependency wait
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+  __syncthreads();
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -302,7 +306,6 @@ int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* 
       if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = B < 148 ? B : 148;
-  kern<<<grid, 320, smem, st>>>(tmW, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(kern, dim3(grid), dim3(320), smem, st, tmW, p));
   return B200_OK;
 }

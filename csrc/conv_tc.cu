@@ -69,6 +69,8 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -224,6 +226,8 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -369,8 +373,7 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
   static bool attr = false;
   if (!attr) { if ((rc = set_smem((const void*)conv_tc_kernel))) return rc; attr = true; }
   dim3 grid(Cout / p.BN, B * p.tiles_h);
-  conv_tc_kernel<<<grid, 192, smem, st>>>(tmA, tmB, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(conv_tc_kernel, grid, dim3(192), smem, st, tmA, tmB, p));
   return B200_OK;
 }
 
@@ -440,8 +443,7 @@ int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias
   if ((rc = act_tmap(&tmDy, dout, B, H, W, Co, 64))) return rc;
   static bool attr = false;
   if (!attr) { if ((rc = set_smem((const void*)conv_wgrad_tc_kernel))) return rc; attr = true; }
-  conv_wgrad_tc_kernel<<<dim3(mtiles, ntile_n, split), 192, smem, st>>>(tmIn, tmDy, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(conv_wgrad_tc_kernel, dim3(mtiles, ntile_n, split), dim3(192), smem, st, tmIn, tmDy, p));
   if (dbias) {
     colsum_bf16_kernel<<<148, Co < 256 ? (Co + 31) / 32 * 32 : 256, 0, st>>>((const bf16*)dout, dbias, (long long)B * H * W, Co);
     B200_LAUNCH_CHECK();

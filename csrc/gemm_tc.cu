@@ -96,6 +96,8 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===== TMA producer: the whole warp walks the loop (uniform control flow), one elected lane issues =====
@@ -262,7 +264,6 @@ extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N,
   }
   B200_REQUIRE(smem <= 200 * 1024, "gemm_tc: %zu bytes of shared memory needed", smem);
   dim3 grid((N + block_n - 1) / block_n, (M + BM - 1) / BM, split_k);
-  gemm_tc_kernel<<<grid, 192, smem, (cudaStream_t)stream>>>(tmA, tmB, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(gemm_tc_kernel, grid, dim3(192), smem, (cudaStream_t)stream, tmA, tmB, p));
   return B200_OK;
 }

@@ -19,6 +19,8 @@ __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __rest
                                                              int bump_step, float* loss_ring, int* correct_ring, int ring) {
   __shared__ float img[32][33];
   const int b = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   if (bump_step && b == 0 && blockIdx.y == 0 && threadIdx.x == 0 && step_ptr) {
     const int s = *step_ptr + 1;          // the step that starts now
     *step_ptr = s;
@@ -74,6 +76,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
                                                           float* __restrict__ dw, float* __restrict__ dbias, int B, int C1) {
   __shared__ float img[32][33];
   __shared__ float red[8][26][32];
+  pdl_wait();
+  pdl_launch_dependents();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   for (int c0 = 0; c0 < C1; c0 += 32) {
     const int c = c0 + lane;
@@ -150,6 +154,8 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
   extern __shared__ float hs[];            // D floats: bf16-rounded h, then (optionally) a copy of W2
   __shared__ float part[8][NC_MAX];
   __shared__ float dl[NC_MAX];
+  pdl_wait();
+  pdl_launch_dependents();
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   // W2 ([D,NC] bf16, 20 KB for the MNIST head) is read twice per row with a stride the coalescer dislikes:
@@ -249,6 +255,8 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const bf16* __restrict_
                                                          float* __restrict__ db2, float* __restrict__ db1, int B, int D, int NC) {
   __shared__ float red[32][8][NC_MAX + 1];
   extern __shared__ float dls[];                                // B x NC dlogits, staged once per block
+  pdl_wait();
+  pdl_launch_dependents();
   for (int i = threadIdx.x; i < B * NC; i += blockDim.x) dls[i] = dlogits[i];
   __syncthreads();
   const int jj = threadIdx.x & 7, bl = threadIdx.x >> 3;       // 8 columns x 32 batch lanes
@@ -292,6 +300,8 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const bf16* __rest
                                                               const uint8_t* __restrict__ argmax, bf16* __restrict__ dy,
                                                               float* __restrict__ dbias, int HP, int WP, int C, long long total) {
   __shared__ float red[256];
+  pdl_wait();
+  pdl_launch_dependents();
   float bsum = 0.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -533,9 +543,8 @@ extern "C" {
 int b200_conv1_pool_fwd(const float* x, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int C1,
                         int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1: bad shape B=%d C1=%d", B, C1);
-  conv1_pool_fwd_kernel<<<dim3(B, 4), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)w, (const bf16*)bias, (bf16*)out, argmax, C1,
-                                                            step_ptr, bump_step, loss_ring, correct_ring, ring);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(conv1_pool_fwd_kernel, dim3(B, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)w, (const bf16*)bias,
+                        (bf16*)out, argmax, C1, step_ptr, bump_step, loss_ring, correct_ring, ring));
   return B200_OK;
 }
 
@@ -543,8 +552,8 @@ int b200_conv1_wgrad(const float* x, const void* da1, const void* a1, const uint
                      int B, int C1, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1 wgrad: bad shape");
   const int grid = B < 74 ? B : 74;          // several images per block: one atomic flush per block, not per image
-  conv1_wgrad_kernel<<<dim3(grid, 4), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)da1, (const bf16*)a1, argmax, dw, dbias, B, C1);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(conv1_wgrad_kernel, dim3(grid, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)da1, (const bf16*)a1,
+                        (const uint8_t*)argmax, dw, dbias, B, C1));
   return B200_OK;
 }
 
@@ -563,10 +572,9 @@ int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, 
     B200_CHECK(cudaFuncSetAttribute(head_fwd_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set = true;
   }
-  head_fwd_bwd_kernel<16><<<B, 256, smem, (cudaStream_t)stream>>>(z, (const bf16*)b1, (const bf16*)w2, (const bf16*)b2, labels,
-                                                                 (bf16*)h, (bf16*)dz, dlogits, logits_out, loss_sum, correct, B,
-                                                                 D, NC, drop_rate, training, seed, step_ptr, layer_id, zero_z, ring, stage_w2);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(head_fwd_bwd_kernel<16>, dim3(B), dim3(256), smem, (cudaStream_t)stream, z, (const bf16*)b1, (const bf16*)w2,
+                        (const bf16*)b2, labels, (bf16*)h, (bf16*)dz, dlogits, logits_out, loss_sum, correct, B, D, NC, drop_rate,
+                        training, seed, step_ptr, layer_id, zero_z, ring, stage_w2));
   return B200_OK;
 }
 
@@ -574,8 +582,8 @@ int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* 
                     int NC, void* stream) {
   B200_REQUIRE(NC >= 1 && NC <= 16, "head wgrad: NC=%d outside [1,16]", NC);
   B200_REQUIRE((size_t)B * NC * 4 <= 40 * 1024, "head wgrad: batch %d too large for the staged dlogits", B);
-  head_wgrad_kernel<16><<<cdiv(D, 8), 256, (size_t)B * NC * sizeof(float), (cudaStream_t)stream>>>((const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(head_wgrad_kernel<16>, dim3(cdiv(D, 8)), dim3(256), (size_t)B * NC * sizeof(float), (cudaStream_t)stream,
+                        (const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC));
   return B200_OK;
 }
 
@@ -588,9 +596,8 @@ int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* a
     while (grid > 1 && (256LL * grid) % C != 0) --grid;
     B200_REQUIRE((256LL * grid) % C == 0, "unpool: cannot build a channel-stable stride for C=%d", C);
   }
-  unpool_relu_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)dpool, (const bf16*)pooled, argmax, (bf16*)dy, dbias,
-                                                                 HP, WP, C, total);
-  B200_LAUNCH_CHECK();
+  B200_CHECK(launch_pdl(unpool_relu_bwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const bf16*)dpool, (const bf16*)pooled,
+                        argmax, (bf16*)dy, dbias, HP, WP, C, total));
   return B200_OK;
 }
 

@@ -1,5 +1,7 @@
 // Host-side runtime helpers: topology discovery (what Open MPI/Horovod learn at MPI_Init,
 // horovod/tensorflow_mnist.py:90) — GPUs, SM counts, memory, and the peer-access (NVLink/NVSwitch) matrix.
+#include <stdlib.h>
+
 #include <string>
 
 #include "../include/b200dp.h"
@@ -52,3 +54,14 @@ extern "C" int b200_topology_json(char* buf, int buflen) {
   memcpy(buf, s.c_str(), s.size() + 1);
   return (int)s.size();
 }
+
+// PDL switch (default on; B200DP_PDL=0 or b200_set_pdl(0) turns every launch back into an ordinary one).
+static int g_pdl = -1;
+int b200_pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("B200DP_PDL");
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl;
+}
+extern "C" int b200_set_pdl(int on) { g_pdl = on ? 1 : 0; return 0; }

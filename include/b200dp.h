@@ -145,6 +145,8 @@ int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias
 /* JSON description of the visible GPUs: names, SM counts, memory, peer-access matrix. Returns bytes written. */
 int b200_topology_json(char* buf, int buflen);
 int b200_l2_flush(void* scratch, size_t bytes, void* stream);
+/* Programmatic dependent launch for the step kernels (default on; also B200DP_PDL=0). */
+int b200_set_pdl(int on);
 
 #ifdef __cplusplus
 }
