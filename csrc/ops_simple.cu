@@ -581,7 +581,12 @@ int b200_head_fwd_bwd(float* z, const void* b1, const void* w2, const void* b2, 
 int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* dw2, float* db2, float* db1, int B, int D,
                     int NC, void* stream) {
   B200_REQUIRE(NC >= 1 && NC <= 16, "head wgrad: NC=%d outside [1,16]", NC);
-  B200_REQUIRE((size_t)B * NC * 4 <= 40 * 1024, "head wgrad: batch %d too large for the staged dlogits", B);
+  B200_REQUIRE((size_t)B * NC * 4 <= 160 * 1024, "head wgrad: batch %d too large for the staged dlogits", B);
+  static bool wg_attr = false;
+  if (!wg_attr) {
+    B200_CHECK(cudaFuncSetAttribute(head_wgrad_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    wg_attr = true;
+  }
   B200_CHECK(launch_pdl(head_wgrad_kernel<16>, dim3(cdiv(D, 8)), dim3(256), (size_t)B * NC * sizeof(float), (cudaStream_t)stream,
                         (const bf16*)h, (const bf16*)dz, dlogits, dw2, db2, db1, B, D, NC));
   return B200_OK;

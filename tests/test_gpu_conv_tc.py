@@ -32,7 +32,7 @@ def _setup(B, H, Ci, Co, k, seed):
     return x, w, b, xr, wr
 
 
-@pytest.mark.parametrize("B,H,Ci,Co,k", [(2, 14, 32, 64, 5), (128, 14, 32, 64, 5), (3, 14, 64, 128, 5), (2, 14, 192, 384, 5), (4, 12, 32, 64, 3), (100, 14, 32, 64, 5)])
+@pytest.mark.parametrize("B,H,Ci,Co,k", [(2, 14, 32, 64, 5), (128, 14, 32, 64, 5), (3, 14, 64, 128, 5), (2, 14, 192, 384, 5), (4, 12, 32, 64, 3), (100, 14, 32, 64, 5), (700, 14, 32, 64, 5)])
 def test_conv_tc_fwd_pool(B, H, Ci, Co, k):
     x, w, b, xr, wr = _setup(B, H, Ci, Co, k, 1)
     pre = F.relu(F.conv2d(xr, wr, b.float(), padding=k // 2))
@@ -53,7 +53,7 @@ def test_conv_tc_fwd_pool(B, H, Ci, Co, k):
     assert torch.equal(picked, pooled.float())
 
 
-@pytest.mark.parametrize("B,H,Ci,Co,k", [(2, 14, 32, 64, 5), (128, 14, 32, 64, 5), (3, 14, 64, 128, 5), (2, 14, 192, 384, 5), (4, 12, 32, 64, 3)])
+@pytest.mark.parametrize("B,H,Ci,Co,k", [(2, 14, 32, 64, 5), (128, 14, 32, 64, 5), (3, 14, 64, 128, 5), (2, 14, 192, 384, 5), (4, 12, 32, 64, 3), (700, 14, 32, 64, 5)])
 def test_conv_tc_dgrad_wgrad(B, H, Ci, Co, k):
     x, w, b, xr, wr = _setup(B, H, Ci, Co, k, 2)
     dy = torch.randn(B, H, H, Co, device="cuda").to(bf16)

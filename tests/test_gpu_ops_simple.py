@@ -52,7 +52,7 @@ def test_conv1_pool_fwd_and_wgrad(B, C1):
     close(db, br.grad, 2e-2, 1e-3 * B)
 
 
-@pytest.mark.parametrize("B,D,training,rate", [(128, 1024, True, 0.5), (100, 1024, True, 0.5), (7, 256, True, 0.0), (64, 1024, False, 0.5), (4, 6144, True, 0.25)])
+@pytest.mark.parametrize("B,D,training,rate", [(128, 1024, True, 0.5), (1024, 1024, True, 0.5), (100, 1024, True, 0.5), (7, 256, True, 0.0), (64, 1024, False, 0.5), (4, 6144, True, 0.25)])
 def test_head_fwd_bwd_and_wgrad(B, D, training, rate):
     torch.manual_seed(1)
     NC = 10
