@@ -141,8 +141,13 @@ class B200Engine(Engine):
         # ---- activations (plain device memory) --------------------------------------------
         B, dev = self.cap, self.device
         e = lambda *s, dt=bf16: torch.empty(*s, device=dev, dtype=dt)
-        self.x = torch.zeros(B, 784, device=dev)
-        self.y = torch.zeros(B, device=dev, dtype=torch.int32)
+        # two input buffers, one per gradient-buffer parity: the H2D copy of step t+1 (copy stream) runs underneath
+        # step t, whose graph reads the other buffer
+        self._xs = [torch.zeros(B, 784, device=dev) for _ in range(2)]
+        self._ys = [torch.zeros(B, device=dev, dtype=torch.int32) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._in_ready = [torch.cuda.Event() for _ in range(2)]
+        self._buf_free = [torch.cuda.Event() for _ in range(2)]
         self.a1, self.am1 = e(B, 14, 14, self.C1), e(B, 14, 14, self.C1, dt=torch.uint8)
         self.c2 = None if self.tc_conv else e(B, 14, 14, self.C2)
         self.a2, self.am2 = e(B, 7, 7, self.C2), e(B, 7, 7, self.C2, dt=torch.uint8)
@@ -161,6 +166,15 @@ class B200Engine(Engine):
         self.adam: Optional[Adam] = None
         self.set_optimizer(optimizer)
         torch.cuda.synchronize()
+
+    @property
+    def x(self) -> torch.Tensor:
+        """Device input buffer the next step (or an eval) reads."""
+        return self._xs[self.global_step & 1]
+
+    @property
+    def y(self) -> torch.Tensor:
+        return self._ys[self.global_step & 1]
 
     def _solo_arena(self) -> SymmetricArena:
         import ctypes
@@ -342,27 +356,39 @@ class B200Engine(Engine):
         self.launches_per_step = K.LAUNCHES[0] - c0
 
     # ------------------------------------------------------------------------------------ public
-    def _stage_inputs(self, x, y, B: int) -> None:
-        if isinstance(x, torch.Tensor) and x.is_cuda:
-            self.x[:B].copy_(x.reshape(B, 784), non_blocking=True)
-            self.y[:B].copy_(y.reshape(B).to(torch.int32), non_blocking=True)
-            return
-        if isinstance(x, torch.Tensor) and isinstance(y, torch.Tensor) and x.is_pinned() and y.is_pinned() \
-                and x.dtype == torch.float32 and y.dtype == torch.int32:
-            # caller-owned pinned batches go straight over PCIe (caller keeps them alive until the step ran)
-            self.x[:B].copy_(x.reshape(B, 784), non_blocking=True)
-            self.y[:B].copy_(y.reshape(B), non_blocking=True)
-            return
-        px, py, ev = self._pinned[self._pin_i]
-        self._pin_i = (self._pin_i + 1) % len(self._pinned)
-        ev.synchronize()
-        xs = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
-        ys = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y))
-        px[:B].copy_(xs.reshape(B, 784))
-        py[:B].copy_(ys.reshape(B))
-        self.x[:B].copy_(px[:B], non_blocking=True)
-        self.y[:B].copy_(py[:B], non_blocking=True)
-        ev.record()
+    def _stage_inputs(self, x, y, B: int, *, overlap: bool = False) -> None:
+        """Copy a batch into the current input buffer.  ``overlap=True`` (training) issues the copy on the copy
+        stream so it runs underneath the previous step; the main stream then waits on the copy's event."""
+        par = self.global_step & 1
+        dx, dy = self._xs[par], self._ys[par]
+        main = torch.cuda.current_stream()
+        st = self.copy_stream if overlap else main
+        if overlap:
+            st.wait_event(self._buf_free[par])          # the step that last read this buffer has finished
+        with torch.cuda.stream(st):
+            if isinstance(x, torch.Tensor) and x.is_cuda:
+                dx[:B].copy_(x.reshape(B, 784), non_blocking=True)
+                dy[:B].copy_(y.reshape(B).to(torch.int32), non_blocking=True)
+            elif isinstance(x, torch.Tensor) and isinstance(y, torch.Tensor) and x.is_pinned() and y.is_pinned() \
+                    and x.dtype == torch.float32 and y.dtype == torch.int32:
+                # caller-owned pinned batches go straight over PCIe (caller keeps them alive until the step ran)
+                dx[:B].copy_(x.reshape(B, 784), non_blocking=True)
+                dy[:B].copy_(y.reshape(B), non_blocking=True)
+            else:
+                px, py, ev = self._pinned[self._pin_i]
+                self._pin_i = (self._pin_i + 1) % len(self._pinned)
+                ev.synchronize()
+                xs = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
+                ys = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y))
+                px[:B].copy_(xs.reshape(B, 784))
+                py[:B].copy_(ys.reshape(B))
+                dx[:B].copy_(px[:B], non_blocking=True)
+                dy[:B].copy_(py[:B], non_blocking=True)
+                ev.record(st)
+            if overlap:
+                self._in_ready[par].record(st)
+        if overlap:
+            main.wait_event(self._in_ready[par])
 
     def train_step(self, x, y) -> StepResult:
         if self.adam is None:
@@ -370,7 +396,7 @@ class B200Engine(Engine):
         B = int(x.shape[0])
         if B > self.cap:
             raise ValueError(f"batch {B} exceeds the engine's batch_size={self.cap}")
-        self._stage_inputs(x, y, B)
+        self._stage_inputs(x, y, B, overlap=True)
         par = self.global_step & 1
         key = (B, par)
         if self.use_graph and key in self._warm:
@@ -385,6 +411,7 @@ class B200Engine(Engine):
         else:
             self._train_graphable(B, par)
             self._warm.add(key)
+        self._buf_free[par].record(torch.cuda.current_stream())
         self.global_step += 1
         self._shards_stale = bool(self._sharded_ranges)
         slot = self.global_step % RING
@@ -410,6 +437,7 @@ class B200Engine(Engine):
         else:
             self._train_graphable(B, par)
             self._warm.add(key)
+        self._buf_free[par].record(torch.cuda.current_stream())
         self.global_step += 1
         self._shards_stale = bool(self._sharded_ranges)
 
@@ -423,6 +451,7 @@ class B200Engine(Engine):
             self._stage_inputs(x[i:i + B], y[i:i + B], B)
             self._forward(B, False)
             self._head(B, False)
+        self._buf_free[self.global_step & 1].record(torch.cuda.current_stream())
         return StepResult(_LazyScalar(self.eval_loss.clone(), 1.0 / n), _LazyScalar(self.eval_correct.clone()), n)
 
     @torch.no_grad()
@@ -436,6 +465,7 @@ class B200Engine(Engine):
             self._forward(B, False)
             self._head(B, False)
             outs.append(self.logits[:B].clone())
+        self._buf_free[self.global_step & 1].record(torch.cuda.current_stream())
         return torch.cat(outs)
 
     # ------------------------------------------------------------------------------------ state
