@@ -16,6 +16,7 @@ _SIGS = {
     "b200_comm_pad_bytes": (SZ, []),
     "b200_comm_create": (I, [I, I, I, C.POINTER(P)]),
     "b200_comm_set_timeout_ms": (I, [P, D]),
+    "b200_comm_set_debug_skew_ns": (I, [P, C.c_uint]),
     "b200_comm_seg_alloc": (I, [P, SZ, PI, P]),
     "b200_comm_seg_open": (I, [P, I, P]),
     "b200_comm_seg_ptr": (P, [P, I, I]),

@@ -69,6 +69,10 @@ class SymmetricArena:
     def set_timeout_ms(self, ms: float) -> None:
         K.check(K.lib().b200_comm_set_timeout_ms(self.h, float(ms)), "set_timeout")
 
+    def set_debug_skew_ns(self, max_ns: int) -> None:
+        """Race hunting: every barrier arrival is delayed by a pseudo-random time below ``max_ns``."""
+        K.check(K.lib().b200_comm_set_debug_skew_ns(self.h, int(max_ns)), "set_debug_skew")
+
     def alloc(self, nbytes: int) -> int:
         """Collective: every rank must call with the same size, in the same order."""
         nbytes = _round_up(int(nbytes), 256)

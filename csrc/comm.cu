@@ -52,12 +52,14 @@ struct Comm {
   bool emulated = false;
   std::vector<Seg> segs;
   unsigned long long timeout_cycles = 40ull * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
+  uint32_t skew_ns = 0;
   void* emu_args = nullptr;   // device scratch for per-rank argument blocks (emulated only)
 };
 
 struct PadPtrs {
   uint32_t* flags[MAXR];   // every rank's flag array (peer-mapped)
   uint32_t* epochs;        // this rank's epoch counters
+  uint32_t skew_ns;        // debug: pseudo-random delay (< skew_ns) before every barrier arrival, to provoke races
 };
 
 // -------------------------------------------------------------------------------------------
@@ -66,6 +68,12 @@ struct PadPtrs {
 __device__ __forceinline__ void rank_barrier(const PadPtrs& pad, int channel, int bid, int rank, int n,
                                              uint32_t epoch, unsigned long long timeout) {
   __syncthreads();
+  if (pad.skew_ns) {       // race-hunting mode: ranks/blocks reach the barrier at scattered times
+    uint32_t h = (uint32_t)rank * 0x9E3779B9u ^ (uint32_t)bid * 0x85EBCA6Bu ^ epoch * 0xC2B2AE35u;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12;
+    __nanosleep(h % pad.skew_ns);
+    __syncthreads();
+  }
   if ((int)threadIdx.x < n) {
     const int peer = threadIdx.x;
     const size_t slot = ((size_t)channel * MAXB + bid) * MAXR;
@@ -410,6 +418,7 @@ inline char* seg_ptr(Comm* c, int seg, int peer, size_t off) { return (char*)c->
 void fill_pad(Comm* c, int as_rank, PadPtrs* p) {
   for (int r = 0; r < c->n; ++r) p->flags[r] = (uint32_t*)seg_ptr(c, 0, r, 0);
   p->epochs = (uint32_t*)seg_ptr(c, 0, as_rank, PAD_FLAGS_BYTES);
+  p->skew_ns = c->skew_ns;
 }
 
 template <typename Args, typename KReal, typename KEmu, typename... Extra>
@@ -465,6 +474,12 @@ int b200_comm_set_timeout_ms(b200_comm_t h, double ms) {
   int khz = 0;
   B200_CHECK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device));
   c->timeout_cycles = (unsigned long long)(ms * (double)khz);
+  return B200_OK;
+}
+
+// Debug aid: every barrier arrival is preceded by a pseudo-random sleep below max_ns nanoseconds.
+int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns) {
+  ((Comm*)h)->skew_ns = max_ns;
   return B200_OK;
 }
 

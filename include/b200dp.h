@@ -29,6 +29,7 @@ const char* b200_last_error(void);
 size_t b200_comm_pad_bytes(void);
 int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out);
 int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
+int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns);   /* race hunting: random delay before each barrier arrival */
 int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out /* 64 B or NULL */);
 int b200_comm_seg_open(b200_comm_t h, int seg_id, const void* all_handles /* nranks x 64 B */);
 void* b200_comm_seg_ptr(b200_comm_t h, int seg_id, int peer);

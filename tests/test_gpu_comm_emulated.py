@@ -105,6 +105,40 @@ def test_fused_allreduce_adam_steps(n, algo):
         rig.close()
 
 
+@pytest.mark.parametrize("n", [4, 8])
+def test_fused_steps_race_stress_with_rank_skew(n):
+    """Hundreds of back-to-back steps with every barrier arrival delayed by a pseudo-random time (up to 20 us):
+    a fast rank must never overwrite a gradient buffer or a weight slice a slow peer is still reading
+    (double-buffered gradients + epoch flags), and the replicas must stay bitwise identical throughout."""
+    torch.manual_seed(n)
+    N = 4096 * 2 + 320                       # odd-sized second range: unaligned slice tails
+    rig = Rig(n, N)
+    try:
+        rig.a.set_debug_skew_ns(20000)
+        master0 = torch.randn(N, device="cuda")
+        for r in range(n):
+            rig.t(rig.state, 0, torch.float32, r).copy_(master0)
+        pr, mr, vr = master0.clone(), torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        ranges = [(0, 4096, 0, 1), (4096, N - 4096, 1, 1)]
+        base = [torch.randn(N, device="cuda") for _ in range(n)]
+        for step in range(1, 241):
+            par = step & 1
+            rig.set_step(step)
+            for r in range(n):                 # gradient of rank r at this step = base[r] * step (checksummable)
+                rig.t(rig.grad, par * N, torch.float32, r).copy_(base[r] * float(step % 7 + 1))
+            rig.fused(par, ranges, nblocks=6)
+            g = sum(base) * float(step % 7 + 1) / n
+            adam_step_(pr, g, mr, vr, step, lr=1e-3)
+            if step % 60 == 0:
+                torch.cuda.synchronize()
+                w0 = rig.t(rig.w16, 0, bf16, 0, es=2)
+                for r in range(1, n):
+                    assert torch.equal(rig.t(rig.w16, 0, bf16, r, es=2), w0), f"step {step}: rank {r} diverged"
+                assert torch.allclose(w0.float(), pr.to(bf16).float(), rtol=2e-2, atol=2e-3), f"step {step}"
+    finally:
+        rig.close()
+
+
 def test_fused_local_only_path_after_adasum():
     rig = Rig(4, 1024)
     try:

@@ -96,5 +96,15 @@ for s in range(3):
 torch.cuda.synchronize()
 digests = hvd.allgather_object(hashlib.sha256(eng.w16.cpu().view(torch.int16).numpy().tobytes()).hexdigest())
 res["still_identical"] = len(set(digests)) == 1
+# race stress on the real fabric: hundreds of graph-replayed steps with every barrier arrival randomly delayed, so
+# fast ranks run a step ahead of slow ones; the replicas must still agree bit for bit (double-buffered gradients)
+hvd.world().arena.set_debug_skew_ns(30000)
+for s in range(300):
+    eng.train_step(xs[s % 6, r], ys[s % 6, r])
+torch.cuda.synchronize()
+digests = hvd.allgather_object(hashlib.sha256(eng.w16.cpu().view(torch.int16).numpy().tobytes()).hexdigest())
+res["identical_after_skewed_stress"] = len(set(digests)) == 1
+res["stress_loss_finite"] = bool(np.isfinite(eng.train_step(xs[0, r], ys[0, r]).loss_value()))
+hvd.world().arena.set_debug_skew_ns(0)
 json.dump(res, open(os.path.join(out_dir, f"r{r}.json"), "w"))
 hvd.shutdown()
