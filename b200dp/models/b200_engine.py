@@ -214,6 +214,14 @@ class B200Engine(Engine):
         self.comm_dense = [rng(by["dense.kernel"])]
         # dense.kernel's gradient is produced by plain stores (GEMM epilogue), never accumulated: nothing to clear
         self.comm_dense = [(r[0], r[1], r[2], 0) for r in self.comm_dense]
+        # GEMM -> reduce-scatter fusion: the dense wgrad GEMM adds its tiles straight into the owner ranks' buffers over
+        # NVLink (red.add), so the fused kernel finds its slice already summed (range algo 3) and skips the peer reads
+        dk = self.spec.param("dense.kernel")
+        self.gemm_rs = bool(self.reduce and not adasum and self.tc_dense and self.comm_dense[0][2] == autoselect.TWOSHOT
+                            and self.F % self.n == 0 and self.comm_dense[0][0] == dk.offset and self.comm_dense[0][1] == dk.numel
+                            and _env_flag("B200DP_GEMM_RS"))
+        if self.gemm_rs:
+            self.comm_dense = [(dk.offset, dk.numel, 3, 1)]
         self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1.+conv2."])]
         self.adasum = adasum
         self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
@@ -272,7 +280,11 @@ class B200Engine(Engine):
         with torch.cuda.stream(s1):
             K.head_wgrad(self.h[:B], self.dz[:B], self.dlogits[:B], self.pv("out.kernel", g), self.pv("out.bias", g),
                          self.pv("dense.bias", g))
-            if self.tc_dense:
+            if self.gemm_rs:
+                K.gemm_tc_reduce_scatter(self.arena.h, a2f, self.dz[:B], self.seg_grad,
+                                         par * self.T * 4 + self.spec.param("dense.kernel").offset * 4, self.n,
+                                         self.F, self.D, B, a_mn_major=True, b_mn_major=True, block_n=128)
+            elif self.tc_dense:
                 K.gemm_tc(a2f, self.dz[:B], gd, self.F, self.D, B, a_mn_major=True, b_mn_major=True, out_mode=0, block_n=128)
             else:
                 K.gemm_simple(a2f, self.dz[:B], gd, self.F, self.D, B, transA=True)

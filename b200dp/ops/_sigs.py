@@ -50,6 +50,7 @@ _SIGS = {
     "b200_adam_local": (I, [P, P, P, P, P, LL, I, D, D, D, D, I, F, P]),
     "b200_bias_relu_bf16": (I, [P, P, P, I, I, I, P]),
     "b200_gemm_tc": (I, [P, P, P, I, I, I, I, I, I, I, I, I, I, I, P]),
+    "b200_gemm_tc_reduce_scatter": (I, [P, P, P, I, SZ, I, I, I, I, I, I, I, I, I, I, P]),
     "b200_conv_tc_fwd": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, P]),
     "b200_conv_tc_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "b200_conv_tc_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),

@@ -150,6 +150,17 @@ def gemm_tc(A, Bm, Cm, M, N, K, *, a_mn_major=False, b_mn_major=False, out_mode:
                              int(b_mn_major), out_mode, split_k, block_n, _stream()), "gemm_tc")
 
 
+def gemm_tc_reduce_scatter(comm_handle, A, Bm, c_seg: int, c_off: int, nranks: int, M, N, K, *, a_mn_major=False,
+                           b_mn_major=False, block_n=128, lda=None, ldb=None, ldc=None):
+    """D = A.B red.add'ed tile by tile into the owner ranks' fp32 buffers at (c_seg, c_off); rank r owns rows r*M/n..."""
+    lda = lda if lda is not None else A.stride(0)
+    ldb = ldb if ldb is not None else Bm.stride(0)
+    ldc = ldc if ldc is not None else N
+    check(lib().b200_gemm_tc_reduce_scatter(comm_handle, _p(_chk(A, bf16, "A")), _p(_chk(Bm, bf16, "B")), c_seg, c_off, nranks,
+                                            M, N, K, lda, ldb, ldc, int(a_mn_major), int(b_mn_major), block_n, _stream()),
+          "gemm_tc_reduce_scatter")
+
+
 def conv_tc_fwd(inp, w, bias, out, argmax=None, *, relu=True, pool=False):
     B, H, W, Ci = inp.shape
     k, Co = w.shape[0], w.shape[3]

@@ -227,7 +227,7 @@ def main():
             "config": {"model": f"mnist_cnn(conv5x5x{eng.C1}-pool-conv5x5x{eng.C2}-pool-dense{eng.D}-dropout0.5-dense10, "
                                 f"{spec.num_params} params)", "global_batch": B * world_size, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world_size}", "optimizer": "Adam(lr=0.001*size) fused into the NVLink allreduce",
-                       "allreduce": {"dense.kernel": ["oneshot", "twoshot", "nvls"][eng.comm_dense[0][2]],
+                       "allreduce": {"dense.kernel": ["oneshot", "twoshot", "nvls", "gemm+reduce-scatter fused, then two-shot tail"][eng.comm_dense[0][2]],
                                      "rest": ["oneshot", "twoshot", "nvls"][eng.comm_rest[1][2]], "wire": "fp32"},
                        "cuda_graph": bool(eng.use_graph), "tcgen05": {"dense": bool(eng.tc_dense), "conv2": bool(eng.tc_conv)},
                        "l2": f"inputs rotate through a {pool_n * B * 784 * 4 / 1e6:.0f} MB device pool (> 126 MB L2); "

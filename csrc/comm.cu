@@ -94,7 +94,7 @@ __device__ __forceinline__ void rank_barrier(const PadPtrs& pad, int channel, in
 struct Range {
   long long start;    // elements
   long long numel;    // multiple of 4
-  int algo;           // 0 one-shot, 1 two-shot
+  int algo;           // 0 one-shot, 1 two-shot, 3 two-shot on a gradient the producer already reduce-scattered
   int zero_other;     // clear the other-parity gradient buffer over this range
 };
 
@@ -208,9 +208,16 @@ __global__ void __launch_bounds__(512, 2) fused_allreduce_adam_kernel(const Fuse
       chunk = (chunk + 3) / 4 * 4;
       const long long lo = min((long long)a.rank * chunk, rg.numel);
       const long long hi = min(lo + chunk, rg.numel);
+      const bool pre_reduced = rg.algo == 3;   // the producing GEMM already reduce-scattered into the owner (red.add over NVLink)
       for (long long q = tid; q < (hi - lo) / 4; q += nthr) {
         const long long i = rg.start + lo + q * 4;
-        const float4 g = reduce_peers(a, i);
+        float4 g;
+        if (pre_reduced) {
+          g = ld_f4(a.grad[a.rank] + i);
+          g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+        } else {
+          g = reduce_peers(a, i);
+        }
         float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
         adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
         adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);

@@ -65,6 +65,10 @@ struct GemmParams {
   int kb_total, kb_per_split;
   uint32_t tmem_cols;
   int nstage;          // pipeline depth: min(4, k-blocks per CTA) — a short K keeps shared memory small (more CTAs per SM)
+  // out_mode 3 (GEMM -> reduce-scatter): row block r*rows_per_owner.. belongs to rank r; the tile is red.add'ed straight
+  // into that rank's buffer over NVLink, so the reduce-scatter of the gradient allreduce happens tile by tile here
+  float* peerC[B200_MAX_RANKS];
+  int rows_per_owner;
 };
 
 __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
     const int out_mode = p.out_mode, N = p.N, bn = p.bn;
     const bool row_ok = row < p.M;
     bf16* const c16 = (bf16*)p.C + (size_t)row * p.ldc;
-    float* const c32 = (float*)p.C + (size_t)row * p.ldc;
+    float* const c32 = (out_mode == 3 ? p.peerC[min(row / p.rows_per_owner, B200_MAX_RANKS - 1)] : (float*)p.C) + (size_t)row * p.ldc;
     uint32_t r[2][16];
     tmem_ld_32x16(taddr, r[0]);
 #pragma unroll 1
@@ -189,6 +193,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
             for (int j = 0; j < 16; j += 4) {
               const float4 f = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
               if (out_mode == 2) red_add_f4(c32 + col + j, f);
+              else if (out_mode == 3) red_add_sys_f4(c32 + col + j, f);
               else st_f4(c32 + col + j, f);
             }
           }
@@ -199,6 +204,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
               const float f = __uint_as_float(v[j]);
               if (out_mode == 1) c16[col + j] = __float2bfloat16(f);
               else if (out_mode == 2) atomicAdd(c32 + col + j, f);
+              else if (out_mode == 3) atomicAdd_system(c32 + col + j, f);
               else c32[col + j] = f;
             }
           }
@@ -213,12 +219,12 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
 
 }  // namespace
 
-extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
-                            int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream) {
+static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* peerC, int rows_per_owner, int M, int N, int K, int lda,
+                          int ldb, int ldc, int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: bad shape %dx%dx%d", M, N, K);
-  B200_REQUIRE(out_mode >= 0 && out_mode <= 2, "gemm_tc: out_mode %d", out_mode);
+  B200_REQUIRE(out_mode >= 0 && out_mode <= 3, "gemm_tc: out_mode %d", out_mode);
   B200_REQUIRE(split_k >= 1, "gemm_tc: split_k %d", split_k);
-  B200_REQUIRE(split_k == 1 || out_mode == 2, "gemm_tc: split_k > 1 needs out_mode 2 (atomic accumulate)");
+  B200_REQUIRE(split_k == 1 || out_mode >= 2, "gemm_tc: split_k > 1 needs an accumulating out_mode");
   B200_REQUIRE(block_n >= 16 && block_n <= 256 && block_n % 16 == 0, "gemm_tc: block_n %d must be a multiple of 16 in [16,256]", block_n);
   B200_REQUIRE(!b_mn_major || block_n % 64 == 0, "gemm_tc: MN-major B needs block_n %% 64 == 0 (got %d)", block_n);
   B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tc: lda/ldb must be multiples of 8 elements (16 bytes)");
@@ -245,6 +251,10 @@ extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N,
     if ((rc = tc::make_tmap_bf16(&tmB, B, 2, dims, str, box, 128))) return rc;
   }
   GemmParams p;
+  memset(&p, 0, sizeof p);
+  p.rows_per_owner = rows_per_owner > 0 ? rows_per_owner : 1;
+  if (peerC)
+    for (int r = 0; r < B200_MAX_RANKS; ++r) p.peerC[r] = peerC[r];
   p.C = C; p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.a_mn = a_mn_major; p.b_mn = b_mn_major; p.out_mode = out_mode; p.bn = block_n;
   p.kb_total = (K + BK - 1) / BK;
@@ -266,4 +276,29 @@ extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N,
   dim3 grid((N + block_n - 1) / block_n, (M + BM - 1) / BM, split_k);
   B200_CHECK(launch_pdl(gemm_tc_kernel, grid, dim3(192), smem, (cudaStream_t)stream, tmA, tmB, p));
   return B200_OK;
+}
+
+extern "C" int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                            int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream) {
+  B200_REQUIRE(out_mode >= 0 && out_mode <= 2, "gemm_tc: out_mode %d", out_mode);
+  return gemm_tc_launch(A, B, C, nullptr, 0, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, out_mode, split_k, block_n, stream);
+}
+
+// GEMM fused with the reduce-scatter of a gradient allreduce: D = A.B is never stored locally; every 128xBN tile is
+// added (red.add, system scope) into the buffer of the rank that owns those rows, over NVLink, as soon as the tile
+// leaves TMEM.  c_seg/c_off name the [M,N] fp32 accumulation buffer inside a symmetric segment (it must be zero
+// when the step starts); rank r owns rows [r*M/n, (r+1)*M/n).  M must be divisible by the world size.
+extern "C" int b200_gemm_tc_reduce_scatter(b200_comm_t comm, const void* A, const void* B, int c_seg, size_t c_off, int nranks,
+                                           int M, int N, int K, int lda, int ldb, int ldc, int a_mn_major, int b_mn_major,
+                                           int block_n, void* stream) {
+  B200_REQUIRE(nranks >= 1 && nranks <= B200_MAX_RANKS && M % nranks == 0, "gemm_tc_reduce_scatter: M=%d not divisible by %d ranks", M, nranks);
+  B200_REQUIRE(c_off % 16 == 0, "gemm_tc_reduce_scatter: offset not 16-byte aligned");
+  float* peers[B200_MAX_RANKS] = {};
+  for (int r = 0; r < nranks; ++r) {
+    char* base = (char*)b200_comm_seg_ptr(comm, c_seg, r);
+    B200_REQUIRE(base != nullptr, "gemm_tc_reduce_scatter: segment %d is not mapped for rank %d", c_seg, r);
+    peers[r] = (float*)(base + c_off);
+  }
+  for (int r = nranks; r < B200_MAX_RANKS; ++r) peers[r] = peers[nranks - 1];
+  return gemm_tc_launch(A, B, peers[0], peers, M / nranks, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, 3, 1, block_n, stream);
 }

@@ -132,6 +132,13 @@ int b200_bias_relu_bf16(const float* z, const void* bias_bf16, void* out_bf16, i
  *   lda/ldb/ldc are row pitches in elements of the stored matrices. */
 int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                  int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream);
+/* GEMM fused with the reduce-scatter leg of the gradient allreduce (dense wgrad -> owner ranks, tile by tile over
+ * NVLink with red.add at system scope).  The [M,N] fp32 buffer at (c_seg, c_off) of every rank must be zero when
+ * the step starts; rank r ends up holding the cross-rank SUM of rows [r*M/n, (r+1)*M/n).  Pair it with range
+ * algo 3 of b200_fused_allreduce_adam.  (horovod/tensorflow_mnist.py:133-136: gradient of layers.dense -> allreduce) */
+int b200_gemm_tc_reduce_scatter(b200_comm_t comm, const void* A, const void* B, int c_seg, size_t c_off, int nranks,
+                                int M, int N, int K, int lda, int ldb, int ldc, int a_mn_major, int b_mn_major,
+                                int block_n, void* stream);
 /* Implicit-GEMM 5x5/3x3 SAME convolution on tensor cores, taps applied by shifted TMA boxes (no im2col buffer).
  *   mode 0 forward: out = relu(conv(in, w) + bias), optionally followed by maxpool2 (+argmax)
  *   mode 1 dgrad  : din = conv_transpose(dout, w)  */

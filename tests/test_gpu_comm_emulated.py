@@ -139,6 +139,46 @@ def test_fused_steps_race_stress_with_rank_skew(n):
         rig.close()
 
 
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_gemm_reduce_scatter_then_fused_adam(n):
+    """GEMM -> reduce-scatter fusion: every rank's wgrad GEMM adds its tiles into the owner ranks' buffers; the fused
+    kernel (range algo 3) then updates each owned slice without reading peers."""
+    torch.manual_seed(n + 7)
+    M, Nn, Kk = 128 * n, 128, 96
+    N = M * Nn
+    rig = Rig(n, N)
+    try:
+        master0 = torch.randn(N, device="cuda")
+        prods = []
+        for r in range(n):
+            rig.t(rig.state, 0, torch.float32, r).copy_(master0)
+            rig.t(rig.grad, 0, torch.float32, r).zero_()
+        for r in range(n):                       # "rank r" runs its GEMM; the epilogue scatters rows to their owners
+            A = torch.randn(Kk, M, device="cuda").to(bf16)        # stored [K, M]  (activations^T, MN-major)
+            Bm = torch.randn(Kk, Nn, device="cuda").to(bf16)      # stored [K, N]
+            prods.append(A.float().t() @ Bm.float())
+            K.gemm_tc_reduce_scatter(rig.a.h, A, Bm, rig.grad, 0, n, M, Nn, Kk, a_mn_major=True, b_mn_major=True, block_n=128)
+        torch.cuda.synchronize()
+        total = sum(prods)
+        rows = M // n
+        for o in range(n):
+            got = rig.t(rig.grad, 0, torch.float32, o).view(M, Nn)
+            assert torch.allclose(got[o * rows:(o + 1) * rows], total[o * rows:(o + 1) * rows], rtol=1e-3, atol=1e-2), f"owner {o}"
+            rest = torch.cat([got[:o * rows], got[(o + 1) * rows:]])
+            assert torch.count_nonzero(rest).item() == 0                  # nothing lands outside the owned rows
+        rig.set_step(1)
+        rig.fused(0, [(0, N, 3, 1)])
+        torch.cuda.synchronize()
+        pr, mr, vr = master0.clone(), torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        adam_step_(pr, total.reshape(-1) / n, mr, vr, 1, lr=1e-3)
+        w0 = rig.t(rig.w16, 0, bf16, 0, es=2)
+        for r in range(n):
+            assert torch.equal(rig.t(rig.w16, 0, bf16, r, es=2), w0)
+        assert torch.allclose(w0.float(), pr.to(bf16).float(), rtol=1e-2, atol=1e-3)
+    finally:
+        rig.close()
+
+
 def test_fused_local_only_path_after_adasum():
     rig = Rig(4, 1024)
     try:

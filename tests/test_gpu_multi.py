@@ -41,6 +41,7 @@ def _check(res, np_, algo):
         assert r0["oracle_cos"] > 0.9 and r0["adam_m_cos"] > 0.95, r0
     if algo == "twoshot":
         assert r0["sharded_ranges"] >= 1
+        assert r0["gemm_rs"] and 3 in r0["algos"], r0           # dense wgrad GEMM fused with its reduce-scatter
     if algo == "nvls" and r0.get("nvls_supported"):
         assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
 

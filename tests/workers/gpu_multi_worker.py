@@ -68,6 +68,7 @@ digests = hvd.allgather_object(digest)
 res["replicas_bitwise_identical"] = len(set(digests)) == 1
 res["sharded_ranges"] = len(eng._sharded_ranges)
 res["engine_nvls"] = bool(eng.nvls)
+res["gemm_rs"] = bool(eng.gemm_rs)
 res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
 # rank 0 alone takes a checkpoint (one-sided gather of sharded Adam state) while the others wait at a barrier
