@@ -39,15 +39,16 @@ def _check(res, np_, algo):
     assert r0["ckpt_step"] == 6
     if algo != "adasum":
         assert r0["oracle_cos"] > 0.9 and r0["adam_m_cos"] > 0.95, r0
-    if algo == "twoshot":
+    if algo in ("twoshot", "gemm_rs"):
         assert r0["sharded_ranges"] >= 1
+    if algo == "gemm_rs":
         assert r0["gemm_rs"] and 3 in r0["algos"], r0           # dense wgrad GEMM fused with its reduce-scatter
     if algo == "nvls" and r0.get("nvls_supported"):
         assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
 
 
 @pytest.mark.multigpu(2)
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum", "nvls"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_two_gpus(tmp_path, algo):
     _check(_run(2, algo, tmp_path), 2, algo)
 
@@ -59,6 +60,6 @@ def test_four_gpus(tmp_path, algo):
 
 
 @pytest.mark.multigpu(8)
-@pytest.mark.parametrize("algo", ["auto", "twoshot", "adasum", "nvls"])
+@pytest.mark.parametrize("algo", ["auto", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_eight_gpus(tmp_path, algo):
     _check(_run(8, algo, tmp_path), 8, algo)

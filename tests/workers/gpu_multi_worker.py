@@ -13,6 +13,9 @@ from b200dp.parallel.collectives import adasum_tree
 from b200dp.train.engine import TorchEngine
 
 out_dir, algo = sys.argv[1], sys.argv[2]
+if algo == "gemm_rs":                      # two-shot with the dense wgrad GEMM fused with its reduce-scatter
+    os.environ["B200DP_GEMM_RS"] = "1"
+    algo = "twoshot"
 hvd.init(device="cuda")
 r, n = hvd.rank(), hvd.size()
 dev = hvd.device()
