@@ -214,13 +214,13 @@ class B200Engine(Engine):
         self.comm_dense = [rng(by["dense.kernel"])]
         # dense.kernel's gradient is produced by plain stores (GEMM epilogue), never accumulated: nothing to clear
         self.comm_dense = [(r[0], r[1], r[2], 0) for r in self.comm_dense]
-        # GEMM -> reduce-scatter fusion (opt-in, B200DP_GEMM_RS=1): the dense wgrad GEMM adds its tiles straight into the
-        # owner ranks' buffers over NVLink (red.add), so the fused kernel finds its slice already summed (range algo 3)
-        # and skips the peer reads.  Measured slower than peer reads at N=2 and N=8 (16-byte remote atomics), see DESIGN.md.
+        # GEMM -> reduce-scatter fusion (B200DP_GEMM_RS=0 disables): the dense wgrad GEMM adds its tiles straight into the
+        # owner ranks' buffers over NVLink (bulk reduce-stores), so the fused kernel finds its slice already summed
+        # (range algo 3) and skips the peer reads.  +7 % step throughput at N=8 over the peer-read two-shot, see DESIGN.md.
         dk = self.spec.param("dense.kernel")
         self.gemm_rs = bool(self.reduce and not adasum and self.tc_dense and self.comm_dense[0][2] == autoselect.TWOSHOT
                             and self.F % self.n == 0 and self.comm_dense[0][0] == dk.offset and self.comm_dense[0][1] == dk.numel
-                            and _env_flag("B200DP_GEMM_RS", "0"))
+                            and _env_flag("B200DP_GEMM_RS"))
         if self.gemm_rs:
             self.comm_dense = [(dk.offset, dk.numel, 3, 1)]
         self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1.+conv2."])]

@@ -6,6 +6,8 @@
 // horovod/tensorflow_mnist_gpu.py:62-66) — forward, dgrad and wgrad all map onto this kernel
 // through the K-major / MN-major operand switches, so weights and activations are never transposed
 // in memory.
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "../include/b200dp.h"
@@ -69,6 +71,7 @@ struct GemmParams {
   // into that rank's buffer over NVLink, so the reduce-scatter of the gradient allreduce happens tile by tile here
   float* peerC[B200_MAX_RANKS];
   int rows_per_owner;
+  int bulk_rs;         // out_mode 3: 1 = bulk reduce-stores from a shared-memory staging row, 0 = per-thread 16-byte red.add
 };
 
 __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -166,6 +169,41 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
     const bool row_ok = row < p.M;
     bf16* const c16 = (bf16*)p.C + (size_t)row * p.ldc;
     float* const c32 = (out_mode == 3 ? p.peerC[min(row / p.rows_per_owner, B200_MAX_RANKS - 1)] : (float*)p.C) + (size_t)row * p.ldc;
+    if (out_mode == 3 && p.bulk_rs) {
+      // GEMM -> reduce-scatter, bulk form: each thread parks 64 columns of its row (256 contiguous bytes) in shared
+      // memory and hands them to the TMA unit as ONE reduce-store (cp.reduce.async.bulk ... add.f32) aimed at the
+      // owner rank's buffer — peer memory over NVLink, or local.  256-byte packets instead of 16-byte atomics.
+      float* stg = reinterpret_cast<float*>(smem + NSTAGE * stage_bytes + 256) + (size_t)(q * 32 + lane) * 64;
+      const uint32_t stg_u = smem_u32(stg);
+      for (int c = 0; c < bn; c += 64) {
+#pragma unroll
+        for (int hq = 0; hq < 4; ++hq) {
+          uint32_t rr[16];
+          if (c + hq * 16 < bn) {
+            tmem_ld_32x16(taddr + c + hq * 16, rr);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              *reinterpret_cast<uint4*>(stg + hq * 16 + j) = make_uint4(rr[j], rr[j + 1], rr[j + 2], rr[j + 3]);
+          }
+        }
+        fence_proxy_async();
+        const int col = n0 + c;
+        const int ncol = min(64, min(bn - c, N - col));
+        if (row_ok && ncol > 0) {
+          if (ncol % 4 == 0) {
+            asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(c32 + col), "r"(stg_u),
+                         "r"(ncol * 4)
+                         : "memory");
+          } else {
+            for (int j = 0; j < ncol; ++j) atomicAdd_system(c32 + col + j, stg[j]);
+          }
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // staging row may be overwritten now
+      }
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    } else {
     uint32_t r[2][16];
     tmem_ld_32x16(taddr, r[0]);
 #pragma unroll 1
@@ -210,6 +248,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
           }
         }
       }
+    }
     }
   }
   tc_fence_before();
@@ -266,7 +305,12 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
   p.tmem_cols = cols;
   p.nstage = p.kb_per_split < MAX_STAGE ? p.kb_per_split : MAX_STAGE;
   if (p.nstage < 2) p.nstage = 2;
-  const size_t smem = (size_t)p.nstage * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
+  {
+    const char* e = getenv("B200DP_GEMM_RS_BULK");
+    p.bulk_rs = (out_mode == 3 && !(e && e[0] == '0')) ? 1 : 0;
+  }
+  const size_t smem = (size_t)p.nstage * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/ +
+                      (p.bulk_rs ? 128 * 64 * sizeof(float) : 0);
   static size_t smem_set = 0;
   if (smem > smem_set) {
     B200_CHECK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
