@@ -86,6 +86,7 @@ class B200Engine(Engine):
         self.comm_blocks = comm_blocks
         self.global_step = 0
         self.launches_per_step = 0
+        self._nvtx = _env_flag("B200DP_NVTX", "0")      # NVTX ranges around the phases of a step (for nsys / ncu --nvtx)
 
         L = self.spec.layers
         self.C1 = L[0].args["cout"]
@@ -363,9 +364,17 @@ class B200Engine(Engine):
 
     def _train_graphable(self, B: int, par: int) -> None:
         c0 = K.LAUNCHES[0]
+        nvtx = self._nvtx
+        if nvtx:
+            torch.cuda.nvtx.range_push("b200dp.forward")
         self._forward(B, True)
         self._head(B, True)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("b200dp.backward+allreduce+adam")
         self._backward_and_update(B, par)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         self.launches_per_step = K.LAUNCHES[0] - c0
 
     # ------------------------------------------------------------------------------------ public

@@ -72,10 +72,17 @@ def fusion_threshold_bytes() -> int:
 
 
 class _DistributedTorchOptimizer:
-    """Generic wrapper around any ``torch.optim.Optimizer``."""
+    """Generic wrapper around any ``torch.optim.Optimizer``.
+
+    Gradients are packed into flat buckets in the order backward produces them (reverse parameter order).  A
+    post-accumulate-grad hook on every parameter counts readiness; the moment a bucket is complete its allreduce is
+    launched — asynchronously (gloo ``async_op``) for CPU tensors, on the peer-memory kernels for CUDA tensors — so
+    the reduction of late layers runs underneath the backward of early ones.  ``step()`` waits, unpacks, steps.
+    ``backward_passes_per_step`` > 1 accumulates locally and reduces on the last pass (Horovod's option of that name).
+    """
 
     def __init__(self, optimizer: torch.optim.Optimizer, named_parameters=None, op: C.ReduceOp = C.Average,
-                 bucket_bytes: Optional[int] = None):
+                 bucket_bytes: Optional[int] = None, backward_passes_per_step: int = 1):
         self._opt = optimizer
         self.op = op
         params: List[torch.nn.Parameter] = []
@@ -86,6 +93,20 @@ class _DistributedTorchOptimizer:
         self._bucket_ix = plan_buckets(sizes, bucket_bytes or fusion_threshold_bytes())
         self._rev = list(reversed(params))
         self._synced = False
+        self._passes = max(1, int(backward_passes_per_step))
+        self._pass = 0
+        self._bucket_of = {}
+        for bi, ix in enumerate(self._bucket_ix):
+            for i in ix:
+                self._bucket_of[id(self._rev[i])] = bi
+        self._ready = [0] * len(self._bucket_ix)
+        self._launched = [False] * len(self._bucket_ix)
+        self._pending = {}
+        self.overlapped_launches = 0
+        self._hooks = []
+        if hasattr(torch.Tensor, "register_post_accumulate_grad_hook"):
+            for p in params:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
 
     # torch optimizer surface -------------------------------------------------
     @property
@@ -110,24 +131,62 @@ class _DistributedTorchOptimizer:
         return getattr(self._opt, item)
 
     # -------------------------------------------------------------------------
+    def _on_grad(self, p) -> None:
+        if not _w.is_initialized() or _w.size() == 1:
+            return
+        bi = self._bucket_of.get(id(p))
+        if bi is None:
+            return
+        self._ready[bi] += 1
+        if self._ready[bi] == len(self._bucket_ix[bi]):
+            self._ready[bi] = 0
+            if bi == len(self._bucket_ix) - 1:
+                self._pass += 1                      # the last bucket closes a backward pass
+            last_pass = (self._pass % self._passes == 0) if bi == len(self._bucket_ix) - 1 else ((self._pass + 1) % self._passes == 0)
+            if last_pass and not self._launched[bi]:
+                self._launch(bi)
+                self.overlapped_launches += 1
+
+    def _launch(self, bi: int) -> None:
+        ps = [self._rev[i] for i in self._bucket_ix[bi]]
+        ps = [p for p in ps if p.grad is not None]
+        self._launched[bi] = True
+        if not ps:
+            return
+        dev = ps[0].grad.device
+        flat = torch.cat([p.grad.detach().reshape(-1).float() for p in ps]).to(dev)
+        if self._passes > 1:
+            flat /= self._passes
+        work = None
+        if dev.type == "cpu" and self.op in (C.Average, C.Sum):
+            import torch.distributed as dist
+            work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, async_op=True)
+        else:
+            C.allreduce_(flat, self.op, segments=[p.numel() for p in ps])
+        self._pending[bi] = (work, flat, ps)
+
     def synchronize(self) -> None:
-        """Reduce all gradients now (bucketed, reverse order)."""
-        if _w.size() == 1:
+        """Finish the reduction of every bucket (launching the ones whose hooks never fired) and unpack."""
+        if not _w.is_initialized() or _w.size() == 1:
             self._synced = True
             return
-        for ix in self._bucket_ix:
-            ps = [self._rev[i] for i in ix]
-            ps = [p for p in ps if p.grad is not None]
-            if not ps:
-                continue
-            dev = ps[0].grad.device
-            flat = torch.cat([p.grad.detach().reshape(-1).float() for p in ps]).to(dev)
-            C.allreduce_(flat, self.op, segments=[p.numel() for p in ps])
+        for bi in range(len(self._bucket_ix)):
+            if not self._launched[bi]:
+                self._launch(bi)
+        for bi in sorted(self._pending):
+            work, flat, ps = self._pending[bi]
+            if work is not None:
+                work.wait()
+                if self.op is C.Average:
+                    flat /= _w.size()
             off = 0
             for p in ps:
                 n = p.numel()
                 p.grad.copy_(flat[off:off + n].view_as(p.grad))
                 off += n
+        self._pending.clear()
+        self._launched = [False] * len(self._bucket_ix)
+        self._ready = [0] * len(self._bucket_ix)
         self._synced = True
 
     def step(self, closure=None):
@@ -138,7 +197,8 @@ class _DistributedTorchOptimizer:
 
 
 def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Average, *,
-                         wire_dtype: str = "fp32", algo: str = "auto", bucket_bytes: Optional[int] = None):
+                         wire_dtype: str = "fp32", algo: str = "auto", bucket_bytes: Optional[int] = None,
+                         backward_passes_per_step: int = 1):
     """Horovod-named factory (see module docstring)."""
     if isinstance(optimizer, DistributedAdam):
         return optimizer
@@ -146,5 +206,5 @@ def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Av
         algo = os.environ.get("B200DP_ALLREDUCE_ALGO", algo)
         return DistributedAdam(base=optimizer, op=op, wire_dtype=wire_dtype, algo=algo)
     if isinstance(optimizer, torch.optim.Optimizer):
-        return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes)
+        return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes, backward_passes_per_step)
     raise TypeError(f"cannot wrap optimizer of type {type(optimizer).__name__}")

@@ -154,6 +154,7 @@ class MonitoredTrainingSession:
         self._stop = False
         self._entered = False
         self.last_result: Optional[StepResult] = None
+        self._timeline = None
 
     # -------------------------------------------------------------------------
     def __enter__(self) -> "MonitoredTrainingSession":
@@ -167,10 +168,30 @@ class MonitoredTrainingSession:
                 log.info("checkpoint_restored", path=restored["path"], step=self.engine.global_step)
         for h in self.hooks:
             h.after_create_session(self)
+        # B200DP_TIMELINE=<path> (Horovod: HOROVOD_TIMELINE): Chrome-trace of every kernel of the run, one file per rank.
+        # Tracing needs Python-visible launches, so the step runs eagerly instead of from its CUDA graph.
+        import os
+        tl_path = os.environ.get("B200DP_TIMELINE") or os.environ.get("HOROVOD_TIMELINE")
+        if tl_path and hasattr(self.engine, "use_graph"):
+            from ..utils.timeline import Timeline
+            self.engine.use_graph = False
+            self._timeline = (Timeline(), tl_path)
+            self._timeline[0].__enter__()
         self._entered = True
         return self
 
     def __exit__(self, exc_type, exc, tb) -> bool:
+        if self._timeline is not None:
+            tl, path = self._timeline
+            self._timeline = None
+            tl.__exit__(None, None, None)
+            r = _w.rank() if _w.is_initialized() else 0
+            out = path if path.endswith(".json") and r == 0 else f"{path}.rank{r}.json"
+            try:
+                tl.save_chrome_trace(out)
+                get_logger().info("timeline_saved", path=out, kernels=len(tl.records))
+            except OSError as e:
+                get_logger().warning("timeline_save_failed", error=str(e))
         try:
             if exc_type is None:
                 for h in self.hooks:

@@ -27,7 +27,8 @@ def test_collectives(tmp_path, np_):
     assert len(res) == np_
     for i, d in enumerate(res):
         assert d["rank"] == i and d["size"] == np_ and d["local_size"] == np_
-        for k in ("avg_ok", "sum_ok", "input_untouched", "adasum_ok", "bcast_ok", "replicas_identical"):
+        assert d["overlapped_launches"] >= 3                              # buckets were reduced from the hooks
+        for k in ("avg_ok", "sum_ok", "input_untouched", "adasum_ok", "bcast_ok", "replicas_identical", "accumulation_ok"):
             assert d[k], (i, k)
         assert d["obj"] == 0 and d["gather"] == list(range(np_))
         assert d["bf16_avg"] == pytest.approx((np_ - 1) / 2)

@@ -41,10 +41,25 @@ for step in range(3):
     x = torch.randn(4, 6, generator=torch.Generator().manual_seed(1000 * step + r))
     lin(x).pow(2).mean().backward()
     opt.step()
+res["overlapped_launches"] = opt.overlapped_launches      # buckets reduced from the grad hooks, during backward
 hvd.broadcast_optimizer_state(opt, 0)
 flat = torch.cat([p.detach().flatten() for p in lin.parameters()])
 ref = hvd.broadcast(flat, 0)
 res["replicas_identical"] = bool(torch.equal(flat, ref))
 
+# gradient accumulation: two backward passes per step reduce once, with the mean of the two gradients
+lin2 = torch.nn.Linear(4, 2)
+hvd.broadcast_parameters(lin2.state_dict(), 0)
+opt2 = hvd.DistributedOptimizer(torch.optim.SGD(lin2.parameters(), lr=1.0), backward_passes_per_step=2)
+w0 = lin2.weight.detach().clone()
+xs2 = [torch.randn(3, 4, generator=torch.Generator().manual_seed(50 + 10 * k + r)) for k in range(2)]
+for x in xs2:
+    lin2(x).sum().backward()
+opt2.step()
+exp = torch.zeros_like(w0)
+for rr in range(n):
+    for k in range(2):
+        exp += torch.randn(3, 4, generator=torch.Generator().manual_seed(50 + 10 * k + rr)).sum(0).expand(2, 4)
+res["accumulation_ok"] = bool(torch.allclose(w0 - lin2.weight.detach(), exp / (2 * n), atol=1e-5))
 json.dump(res, open(os.path.join(out_dir, f"r{r}.json"), "w"))
 hvd.shutdown()
