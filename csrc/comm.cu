@@ -457,6 +457,8 @@ void b200_set_error(const char* fmt, ...) {
   g_err = buf;
 }
 
+void b200_forget_mcsegs(void* comm);   // defined with the NVLS code below
+
 extern "C" {
 
 const char* b200_last_error(void) { return g_err.c_str(); }
@@ -552,6 +554,7 @@ int b200_comm_destroy(b200_comm_t h) {
       else if (s.opened[r]) cudaIpcCloseMemHandle(s.base[r]);
     }
   if (c->emu_args) cudaFree(c->emu_args);
+  b200_forget_mcsegs(c);
   delete c;
   return B200_OK;
 }
@@ -970,6 +973,14 @@ struct McSeg {
 };
 std::vector<std::pair<Comm*, McSeg>> g_mcsegs;
 std::mutex g_mc_mu;
+
+}  // namespace
+void b200_forget_mcsegs(void* comm) {
+  std::lock_guard<std::mutex> lk(g_mc_mu);
+  for (size_t i = g_mcsegs.size(); i-- > 0;)
+    if ((void*)g_mcsegs[i].first == comm) g_mcsegs.erase(g_mcsegs.begin() + i);
+}
+namespace {
 
 McSeg* find_mc(Comm* c, int seg) {
   for (auto& e : g_mcsegs)

@@ -92,14 +92,6 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, const float* 
   }
 }
 
-__device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
-  asm volatile(
-      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(
-          smem_u32(dst)),
-      "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-      : "memory");
-}
-
 template <int KK, int KSTEPS, int MODE>
 __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
