@@ -58,7 +58,6 @@ class DistributedAdam:
     """What ``DistributedOptimizer(Adam(...))`` returns: config consumed by engines."""
     base: Adam
     op: C.ReduceOp = C.Average
-    wire_dtype: str = "fp32"          # "fp32" | "bf16" gradients on the wire
     algo: str = "auto"                # auto | oneshot | twoshot | nvls
 
     @property
@@ -197,14 +196,14 @@ class _DistributedTorchOptimizer:
 
 
 def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Average, *,
-                         wire_dtype: str = "fp32", algo: str = "auto", bucket_bytes: Optional[int] = None,
+                         algo: str = "auto", bucket_bytes: Optional[int] = None,
                          backward_passes_per_step: int = 1):
     """Horovod-named factory (see module docstring)."""
     if isinstance(optimizer, DistributedAdam):
         return optimizer
     if isinstance(optimizer, Adam):
         algo = os.environ.get("B200DP_ALLREDUCE_ALGO", algo)
-        return DistributedAdam(base=optimizer, op=op, wire_dtype=wire_dtype, algo=algo)
+        return DistributedAdam(base=optimizer, op=op, algo=algo)
     if isinstance(optimizer, torch.optim.Optimizer):
         return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes, backward_passes_per_step)
     raise TypeError(f"cannot wrap optimizer of type {type(optimizer).__name__}")
