@@ -32,6 +32,7 @@ _SIGS = {
     "b200_comm_mcseg_bind": (I, [P, I]),
     "b200_comm_seg_mc_ptr": (P, [P, I]),
     "b200_allreduce_nvls": (I, [P, I, I, I, I, SZ, I, SZ, LL, F, P]),
+    "b200_broadcast_nvls": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, P]),
     "b200_fused_allreduce_adam_nvls": (I, [P, I, I, I, I, SZ, SZ, I, SZ, SZ, SZ, I, SZ, I, SZ, SZ, F, LL, LL, I, P]),
     "b200_adasum_scratch_bytes": (SZ, [I, I]),
     "b200_adasum_level": (I, [P, I, I, I, I, SZ, I, SZ, I, SZ, I, PLL, PLL, P]),

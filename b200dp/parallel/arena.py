@@ -201,7 +201,11 @@ class SymmetricArena:
         cap = max(fusion_threshold_bytes() // 4, 1 << 16)
         self._staging_elems = _round_up(cap, 64)
         # [src parity 0][src parity 1][dst][adasum ping][adasum pong][scratch]
-        self._staging = self.alloc(self._staging_elems * 4 * 5 + (1 << 20))
+        # B200DP_BCAST=nvls puts the staging buffer behind an NVSwitch multicast object: large broadcasts then leave
+        # the root once and are replicated by the switch
+        self._staging_mc = bool(os.environ.get("B200DP_BCAST", "") == "nvls" and self.nvls_supported())
+        alloc = self.alloc_multicast if self._staging_mc else self.alloc
+        self._staging = alloc(self._staging_elems * 4 * 5 + (1 << 20))
 
     def _launch_shape(self, numel: int) -> Tuple[int, int]:
         nb = max(1, min(32, numel // 8192))
@@ -267,8 +271,13 @@ class SymmetricArena:
             if self.rank == root:
                 self.bytes_view(self._staging)[src_off:src_off + (b1 - b0)].copy_(raw[b0:b1])
             nb, nt = self._launch_shape(n4)
-            K.check(K.lib().b200_broadcast(self.h, CH_BCAST, nb, nt, root, self._staging, src_off, self._staging, dst_off, n4,
-                                           ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "broadcast")
+            st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            if getattr(self, "_staging_mc", False) and n4 * 4 >= (1 << 20):
+                K.check(K.lib().b200_broadcast_nvls(self.h, CH_BCAST, max(nb, 64), nt, root, self._staging, src_off, self._staging,
+                                                    dst_off, n4, st), "broadcast_nvls")
+            else:
+                K.check(K.lib().b200_broadcast(self.h, CH_BCAST, nb, nt, root, self._staging, src_off, self._staging, dst_off, n4,
+                                               st), "broadcast")
             if self.rank != root:
                 raw[b0:b1].copy_(self.bytes_view(self._staging)[dst_off:dst_off + (b1 - b0)])
         return tensor

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--out", default="gpurun_out/sweep.json")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--write-table", action="store_true")
+    ap.add_argument("--only-bcast", action="store_true", help="measure the broadcast arms only")
     a = ap.parse_args()
     os.environ.setdefault("B200DP_LOG_LEVEL", "WARNING")
     hvd.init(device="cuda")
@@ -91,7 +92,7 @@ def main():
         iters = 200 if S <= (1 << 20) else (50 if S <= (1 << 26) else 10)
         nb, nt = shape(numel)
         row = {"bytes": numel * 4}
-        for name, algo in (("oneshot", 0), ("twoshot", 1)):
+        for name, algo in (() if a.only_bcast else (("oneshot", 0), ("twoshot", 1))):
             if algo == 0 and numel * 4 * n > (3 << 30):
                 continue                                   # one-shot reads N*S bytes: pointless at this size
             f = lambda algo=algo: K.check(K.lib().b200_allreduce(arena.h, 5, nb, nt, algo, seg, 0, seg, dst_off, numel, 1.0 / n, stream()))
@@ -103,7 +104,7 @@ def main():
             us = timed(f, iters)
             row[name + "_us"] = us
             row[name + "_busbw_gbs"] = numel * 4 * 2 * (n - 1) / n / us / 1e3
-        if seg_mc is not None and numel * 4 >= 4096:
+        if seg_mc is not None and numel * 4 >= 4096 and not a.only_bcast:
             fn = lambda: K.check(K.lib().b200_allreduce_nvls(arena.h, 7, nb, nt, seg_mc, 0, seg_mc, dst_off, numel, 1.0 / n, stream()))
             fn()
             torch.cuda.synchronize()
@@ -117,19 +118,31 @@ def main():
         us = timed(fb, iters)
         row["bcast_us"] = us
         row["bcast_gbs"] = numel * 4 / us / 1e3
+        if seg_mc is not None and numel * 4 >= 4096:
+            fbn = lambda: K.check(K.lib().b200_broadcast_nvls(arena.h, 8, nb, nt, 0, seg_mc, 0, seg_mc, dst_off, numel, stream()))
+            fbn()
+            torch.cuda.synchronize()
+            got = arena.view(seg_mc, dst_off, numel, torch.float32)
+            assert float(got[0]) == 1.0 and float(got[numel - 1]) == 1.0, ("nvls bcast", S, float(got[0]))
+            us = timed(fbn, iters)
+            row["nvls_bcast_us"] = us
+            row["nvls_bcast_gbs"] = numel * 4 / us / 1e3
         if nccl is not None:
             t = tn[:numel]
-            us = timed(lambda: dist.all_reduce(t, group=nccl), iters)
-            row["nccl_us"] = us
-            row["nccl_busbw_gbs"] = numel * 4 * 2 * (n - 1) / n / us / 1e3
+            if not a.only_bcast:
+                us = timed(lambda: dist.all_reduce(t, group=nccl), iters)
+                row["nccl_us"] = us
+                row["nccl_busbw_gbs"] = numel * 4 * 2 * (n - 1) / n / us / 1e3
             us = timed(lambda: dist.broadcast(t, src=0, group=nccl), iters)
             row["nccl_bcast_us"] = us
             row["nccl_bcast_gbs"] = numel * 4 / us / 1e3
         # roofline: two-shot moves 2(N-1)/N*S per direction per GPU over NVLink
-        best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us", "nvls_us"))
-        row["best_us"] = best
-        row["nvlink_roofline_us"] = numel * 4 * 2 * (n - 1) / n / (PEER_GBS * 1e3)
-        row["frac_of_roofline"] = row["nvlink_roofline_us"] / best
+        cands = [v for k, v in row.items() if k in ("oneshot_us", "twoshot_us", "nvls_us")]
+        if cands:
+            best = min(cands)
+            row["best_us"] = best
+            row["nvlink_roofline_us"] = numel * 4 * 2 * (n - 1) / n / (PEER_GBS * 1e3)
+            row["frac_of_roofline"] = row["nvlink_roofline_us"] / best
         rows.append(row)
         if r == 0:
             print(json.dumps(row), flush=True)

@@ -1086,6 +1086,39 @@ __global__ void __launch_bounds__(512) nvls_allreduce_kernel(const NvlsArgs a) {
   if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
 }
 
+struct NvlsBcastArgs {
+  int rank, n, channel, root;
+  PadPtrs pad;
+  const float* src;       // root's local source
+  float* dst_mc;          // multicast view of the destination
+  long long numel;
+  unsigned long long timeout;
+};
+
+// Broadcast through the switch: the root stores once to the multicast address, the NVSwitch replicates the
+// store into every GPU's copy of the segment.  The root's link carries S bytes, not (N-1)*S.
+__global__ void __launch_bounds__(512) nvls_broadcast_kernel(const NvlsBcastArgs a) {
+  const int bid = blockIdx.x;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);     // destination free, source ready
+  if (a.rank == a.root) {
+    const long long nq = a.numel / 4;
+    for (long long q0 = tid; q0 < nq; q0 += 4 * nthr) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (q0 + u * nthr < nq) v[u] = ld_f4(a.src + (q0 + u * nthr) * 4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (q0 + u * nthr < nq) multimem_st_f4(a.dst_mc + (q0 + u * nthr) * 4, v[u]);
+    }
+    __threadfence_system();
+  }
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);     // data has landed everywhere
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1233,6 +1266,29 @@ int b200_allreduce_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, i
   a.dst_mc = (float*)((char*)ds->mc_base + dst_off);
   a.scale = scale; a.start = 0; a.numel = numel; a.timeout = c->timeout_cycles;
   nvls_allreduce_kernel<<<nblocks, nthreads, 0, (cudaStream_t)stream>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Broadcast root's src into every rank's dst with one multicast store stream (dst must be a bound multicast segment).
+int b200_broadcast_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int root, int src_seg, size_t src_off,
+                        int dst_seg, size_t dst_off, long long numel, void* stream) {
+  Comm* c = (Comm*)h;
+  McSeg* ds = find_mc(c, dst_seg);
+  B200_REQUIRE(ds && ds->mc_base, "broadcast_nvls: destination must be a bound multicast segment");
+  B200_REQUIRE(channel >= 0 && channel < MAXCH && nblocks >= 1 && nblocks <= MAXB && nthreads >= 32 && nthreads <= 512, "bad launch shape");
+  B200_REQUIRE(numel % 4 == 0 && root >= 0 && root < c->n, "broadcast_nvls: bad numel/root");
+  int rc;
+  if ((rc = check_seg(c, src_seg, src_off, numel * 4, "nvls bcast src"))) return rc;
+  if ((rc = check_seg(c, dst_seg, dst_off, numel * 4, "nvls bcast dst"))) return rc;
+  NvlsBcastArgs a;
+  memset(&a, 0, sizeof a);
+  a.rank = c->rank; a.n = c->n; a.channel = channel; a.root = root;
+  fill_pad(c, c->rank, &a.pad);
+  a.src = (const float*)seg_ptr(c, src_seg, c->rank, src_off);
+  a.dst_mc = (float*)((char*)ds->mc_base + dst_off);
+  a.numel = numel; a.timeout = c->timeout_cycles;
+  nvls_broadcast_kernel<<<nblocks, nthreads, 0, (cudaStream_t)stream>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

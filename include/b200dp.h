@@ -64,6 +64,8 @@ int b200_comm_mcseg_bind(b200_comm_t h, int seg_id);
 void* b200_comm_seg_mc_ptr(b200_comm_t h, int seg_id);
 int b200_allreduce_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int src_seg, size_t src_off, int dst_seg,
                         size_t dst_off, long long numel, float scale, void* stream);
+int b200_broadcast_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int root, int src_seg, size_t src_off,
+                        int dst_seg, size_t dst_off, long long numel, void* stream);
 int b200_fused_allreduce_adam_nvls(b200_comm_t h, int channel, int nblocks, int nthreads, int grad_seg, size_t grad_cur_off,
                                    size_t grad_other_off, int state_seg, size_t master_off, size_t m_off, size_t v_off,
                                    int w16_seg, size_t w16_off, int ctrl_seg, size_t step_off, size_t hyper_off, float scale,

@@ -45,6 +45,7 @@ def _check(res, np_, algo):
         assert r0["gemm_rs"] and 3 in r0["algos"], r0           # dense wgrad GEMM fused with its reduce-scatter
     if algo == "nvls" and r0.get("nvls_supported"):
         assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
+        assert r0["bcast_nvls"], r0                                   # and so did the large public broadcasts
 
 
 @pytest.mark.multigpu(2)

@@ -13,6 +13,8 @@ from b200dp.parallel.collectives import adasum_tree
 from b200dp.train.engine import TorchEngine
 
 out_dir, algo = sys.argv[1], sys.argv[2]
+if algo == "nvls":                         # also route large public broadcasts through the switch (multimem.st)
+    os.environ["B200DP_BCAST"] = "nvls"
 if algo == "gemm_rs":                      # two-shot with the dense wgrad GEMM fused with its reduce-scatter
     os.environ["B200DP_GEMM_RS"] = "1"
     algo = "twoshot"
@@ -71,6 +73,7 @@ digests = hvd.allgather_object(digest)
 res["replicas_bitwise_identical"] = len(set(digests)) == 1
 res["sharded_ranges"] = len(eng._sharded_ranges)
 res["engine_nvls"] = bool(eng.nvls)
+res["bcast_nvls"] = bool(getattr(hvd.world().arena, "_staging_mc", False))
 res["gemm_rs"] = bool(eng.gemm_rs)
 res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
