@@ -1,4 +1,5 @@
-"""The sm_100a training engine for the MNIST CNN family.
+"""The sm_100a training engine for both MNIST CNN families (``mnist_cnn`` as coded in the reference scripts, and
+``keras128``, the Keras-example shape BASELINE.json's prose names).
 
 One training step (the reference's ``mon_sess.run(train_op)``, ``horovod/tensorflow_mnist.py:168-171``;
 Keras ``fit`` inner loop, ``horovod/tensorflow_mnist_gpu.py:173``) is a fixed sequence of hand-written
@@ -10,6 +11,10 @@ kernels replayed from a CUDA graph:
         ->  dense dgrad (tcgen05) -> unpool+ReLU mask -> conv2 wgrad / dgrad (tcgen05) -> conv1 wgrad
   comm: per bucket ONE kernel = NVLink allreduce + 1/size + Adam + bf16 weight refresh; the dense
         bucket's kernel runs on a second stream underneath the convolution backward.
+
+``keras128`` runs the same DAG with its own geometry: conv1 3x3 VALID + ReLU (CUDA cores, no pool) -> conv2 3x3 VALID
+implicit GEMM + ReLU + pool (tcgen05, 24x24 output walked in 8x16 tiles) -> dropout 0.25 -> dense 9216x128 -> head
+(dropout 0.5); the feature dropout's backward is folded into the unpool kernel (a dropped activation is a zero there).
 
 All persistent state (fp32 master weights, Adam moments, two gradient buffers, bf16 working
 weights, step counter, hyper-parameters, loss ring) lives in symmetric peer-mapped segments.
@@ -70,8 +75,9 @@ class B200Engine(Engine):
                  use_graph: Optional[bool] = None, dropout: bool = True, use_tc: Optional[bool] = None,
                  comm_blocks: int = 296, arena: Optional[SymmetricArena] = None, **_ignored):
         self.spec = spec or get_spec()
-        if self.spec.arch != "mnist_cnn":
-            raise NotImplementedError(f"B200Engine implements the mnist_cnn family; use engine='torch' for {self.spec.arch}")
+        if self.spec.arch not in ("mnist_cnn", "keras128"):
+            raise NotImplementedError(f"B200Engine implements mnist_cnn and keras128; use engine='torch' for {self.spec.arch}")
+        self.keras = self.spec.arch == "keras128"
         if not torch.cuda.is_available():
             raise RuntimeError("B200Engine needs a CUDA device")
         K.lib()                                     # fail loudly if the extension is missing
@@ -90,9 +96,24 @@ class B200Engine(Engine):
 
         L = self.spec.layers
         self.C1 = L[0].args["cout"]
-        self.C2 = L[2].args["cout"]
+        self.K1 = L[0].args["k"]
+        if self.keras:
+            # conv(VALID) conv(VALID) pool dropout flatten dense dropout dense
+            self.C2, self.K2, self.PAD2 = L[1].args["cout"], L[1].args["k"], 0
+            self.H1 = 28 - self.K1 + 1                     # conv1 output (no pool): 26
+            self.H2 = self.H1 - self.K2 + 1                # conv2 output: 24
+            self.feat_drop = L[3].args["rate"]             # Dropout(0.25) on the pooled features, Philox layer 0
+            self.head_layer = 1                            # Dropout(0.5) after dense: Philox layer 1
+        else:
+            # conv(SAME) pool conv(SAME) pool flatten dense dropout dense
+            self.C2, self.K2, self.PAD2 = L[2].args["cout"], L[2].args["k"], L[2].args["k"] // 2
+            self.H1 = 14                                   # conv1 output after its pool
+            self.H2 = 14
+            self.feat_drop = 0.0
+            self.head_layer = 0
+        self.HP = self.H2 // 2                             # pooled conv2 output: 7 / 12
         self.D = L[5].args["units"]
-        self.F = 7 * 7 * self.C2
+        self.F = self.HP * self.HP * self.C2
         self.NC = self.spec.num_classes
         self.drop_rate = L[6].args["rate"]
         if self.tc_conv and (self.C1 % 32 or self.C2 % 64):
@@ -149,13 +170,15 @@ class B200Engine(Engine):
         self.copy_stream = torch.cuda.Stream(device=dev)
         self._in_ready = [torch.cuda.Event() for _ in range(2)]
         self._buf_free = [torch.cuda.Event() for _ in range(2)]
-        self.a1, self.am1 = e(B, 14, 14, self.C1), e(B, 14, 14, self.C1, dt=torch.uint8)
-        self.c2 = None if self.tc_conv else e(B, 14, 14, self.C2)
-        self.a2, self.am2 = e(B, 7, 7, self.C2), e(B, 7, 7, self.C2, dt=torch.uint8)
+        H1, H2, HP = self.H1, self.H2, self.HP
+        self.a1 = e(B, H1, H1, self.C1)
+        self.am1 = None if self.keras else e(B, H1, H1, self.C1, dt=torch.uint8)
+        self.c2 = None if self.tc_conv else e(B, H2, H2, self.C2)
+        self.a2, self.am2 = e(B, HP, HP, self.C2), e(B, HP, HP, self.C2, dt=torch.uint8)
         self.z = torch.zeros(B, self.D, device=dev)
         self.h, self.dz = e(B, self.D), e(B, self.D)
         self.dlogits, self.logits = e(B, self.NC, dt=torch.float32), e(B, self.NC, dt=torch.float32)
-        self.dpool, self.dy2, self.da1 = e(B, 7, 7, self.C2), e(B, 14, 14, self.C2), e(B, 14, 14, self.C1)
+        self.dpool, self.dy2, self.da1 = e(B, HP, HP, self.C2), e(B, H2, H2, self.C2), e(B, H1, H1, self.C1)
         self._pinned = [(torch.empty(B, 784).pin_memory(), torch.empty(B, dtype=torch.int32).pin_memory(), torch.cuda.Event())
                         for _ in range(3)]
         self._pin_i = 0
@@ -231,16 +254,23 @@ class B200Engine(Engine):
     # ------------------------------------------------------------------------------------ kernels
     def _forward(self, B: int, training: bool) -> None:
         w = self.w16
-        x, a1, am1, a2, am2 = self.x[:B], self.a1[:B], self.am1[:B], self.a2[:B], self.am2[:B]
-        K.conv1_pool_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1, am1,
-                         self.step_dev if training else None, bump_step=training,
-                         loss_ring=self.loss_ring if training else None, correct_ring=self.correct_ring if training else None)
+        x, a1, a2, am2 = self.x[:B], self.a1[:B], self.a2[:B], self.am2[:B]
+        ring = dict(loss_ring=self.loss_ring if training else None, correct_ring=self.correct_ring if training else None)
+        if self.keras:
+            K.conv1_valid_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1,
+                              self.step_dev if training else None, bump_step=training, **ring)
+        else:
+            K.conv1_pool_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1, self.am1[:B],
+                             self.step_dev if training else None, bump_step=training, **ring)
         k2, b2 = self.pv("conv2.kernel", w), self.pv("conv2.bias", w)
         if self.tc_conv:
-            K.conv_tc_fwd(a1, k2, b2, a2, am2, relu=True, pool=True)
+            K.conv_tc_fwd(a1, k2, b2, a2, am2, relu=True, pool=True, pad=self.PAD2)
         else:
-            K.conv_direct_fwd(a1, k2, b2, self.c2[:B], 2, relu=True)
+            K.conv_direct_fwd(a1, k2, b2, self.c2[:B], self.PAD2, relu=True)
             K.maxpool_fwd(self.c2[:B], a2, am2)
+        if training and self.dropout and self.feat_drop > 0:
+            # Keras Dropout(0.25) between the pool and Flatten, in place; its backward rides in the unpool kernel
+            K.dropout_bf16(a2, a2, self.feat_drop, self.seed, self.step_dev, 0)
         a2f = a2.view(B, self.F)
         wd = self.pv("dense.kernel", w)
         if self.tc_dense:
@@ -255,7 +285,7 @@ class B200Engine(Engine):
             K.head_fwd_bwd(self.z[:B], self.pv("dense.bias", w), self.pv("out.kernel", w), self.pv("out.bias", w), self.y[:B],
                            self.h[:B], self.dz[:B], self.dlogits[:B], None, self.loss_ring, self.correct_ring,
                            drop_rate=self.drop_rate if self.dropout else 0.0, training=True, seed=self.seed,
-                           step_ptr=self.step_dev, zero_z=True, ring=RING)
+                           step_ptr=self.step_dev, layer_id=self.head_layer, zero_z=True, ring=RING)
         else:
             K.head_fwd_bwd(self.z[:B], self.pv("dense.bias", w), self.pv("out.kernel", w), self.pv("out.bias", w), self.y[:B],
                            self.h[:B], None, None, self.logits[:B], self.eval_loss, self.eval_correct,
@@ -304,23 +334,27 @@ class B200Engine(Engine):
                 self._comm(0, self.comm_dense, par)
         ev_s1 = torch.cuda.Event()
         ev_s1.record(s1)
-        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B], self.pv("conv2.bias", g))
+        gscale = 1.0 / (1.0 - self.feat_drop) if (self.dropout and self.feat_drop > 0) else 1.0
+        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B], self.pv("conv2.bias", g), gscale=gscale)
         ev_dy = torch.cuda.Event()
         ev_dy.record(main)
         k2 = self.pv("conv2.kernel", w)
         s2.wait_event(ev_dy)
         with torch.cuda.stream(s2):
             if self.tc_conv:
-                K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None)
+                K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
             else:
-                K.conv_direct_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, 2)
+                K.conv_direct_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, self.PAD2)
             ev_s2 = torch.cuda.Event()
             ev_s2.record(s2)
         if self.tc_conv:
-            K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B])
+            K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B], pad=self.PAD2)
         else:
-            K.conv_direct_dgrad(self.dy2[:B], k2, self.da1[:B], 2)
-        K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+            K.conv_direct_dgrad(self.dy2[:B], k2, self.da1[:B], self.PAD2)
+        if self.keras:
+            K.conv1_valid_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        else:
+            K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
         main.wait_event(ev_s2)
         main.wait_event(ev_s1)
         if self.adasum:

@@ -43,6 +43,10 @@ _SIGS = {
     "b200_head_wgrad": (I, [P, P, P, P, P, P, I, I, I, P]),
     "b200_unpool_relu_bwd": (I, [P, P, P, P, P, I, I, I, I, P]),
     "b200_maxpool_fwd": (I, [P, P, P, I, I, I, I, P]),
+    "b200_unpool_relu_bwd_scaled": (I, [P, P, P, P, P, I, I, I, I, F, P]),
+    "b200_conv1_valid_fwd": (I, [P, P, P, P, I, I, I, P, I, P, P, I, P]),
+    "b200_conv1_valid_wgrad": (I, [P, P, P, P, P, I, I, I, P]),
+    "b200_dropout_bf16": (I, [P, P, LL, F, U64, P, I, P]),
     "b200_conv_direct_fwd": (I, [P, P, P, P, I, I, I, I, I, I, I, I, P]),
     "b200_conv_direct_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, P]),
     "b200_conv_direct_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
@@ -55,6 +59,9 @@ _SIGS = {
     "b200_conv_tc_fwd": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, P]),
     "b200_conv_tc_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "b200_conv_tc_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "b200_conv_tc_fwd_pad": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P]),
+    "b200_conv_tc_dgrad_pad": (I, [P, P, P, I, I, I, I, I, I, I, P]),
+    "b200_conv_tc_wgrad_pad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
     "b200_topology_json": (I, [C.c_char_p, I]),
     "b200_l2_flush": (I, [P, SZ, P]),
     "b200_set_pdl": (I, [I]),

@@ -80,10 +80,31 @@ def head_wgrad(h, dz, dlogits, dw2, db2, db1):
                                 _p(dw2), _p(db2), _p(db1), B, D, NC, _stream()), "head_wgrad")
 
 
-def unpool_relu_bwd(dpool, pooled, argmax, dy, dbias=None):
+def unpool_relu_bwd(dpool, pooled, argmax, dy, dbias=None, gscale: float = 1.0):
     B, HP, WP, Cc = pooled.shape
-    check(lib().b200_unpool_relu_bwd(_p(_chk(dpool, bf16, "dpool")), _p(_chk(pooled, bf16, "pooled")), _p(argmax), _p(_chk(dy, bf16, "dy")),
-                                     _p(dbias), B, HP, WP, Cc, _stream()), "unpool_relu_bwd")
+    check(lib().b200_unpool_relu_bwd_scaled(_p(_chk(dpool, bf16, "dpool")), _p(_chk(pooled, bf16, "pooled")), _p(argmax),
+                                            _p(_chk(dy, bf16, "dy")), _p(dbias), B, HP, WP, Cc, float(gscale), _stream()), "unpool_relu_bwd")
+
+
+def conv1_valid_fwd(x, w, bias, out, step_ptr: Optional[torch.Tensor] = None, bump_step: bool = False,
+                    loss_ring: Optional[torch.Tensor] = None, correct_ring: Optional[torch.Tensor] = None):
+    """keras128 first layer: k x k VALID conv of the 28x28 image + bias + ReLU -> [B, 28-k+1, 28-k+1, C1] bf16."""
+    B, k, C1 = x.shape[0], w.shape[0], w.shape[-1]
+    _chk(x, torch.float32, "x"); _chk(w, bf16, "w"); _chk(bias, bf16, "bias"); _chk(out, bf16, "out")
+    check(lib().b200_conv1_valid_fwd(_p(x), _p(w), _p(bias), _p(out), B, C1, k, _p(step_ptr), int(bump_step), _p(loss_ring),
+                                     _p(correct_ring), 0 if loss_ring is None else loss_ring.numel(), _stream()), "conv1_valid_fwd")
+
+
+def conv1_valid_wgrad(x, da1, a1, dw, dbias):
+    B, k, C1 = x.shape[0], dw.shape[0], a1.shape[-1]
+    check(lib().b200_conv1_valid_wgrad(_p(_chk(x, torch.float32, "x")), _p(_chk(da1, bf16, "da1")), _p(_chk(a1, bf16, "a1")),
+                                       _p(_chk(dw, torch.float32, "dw")), _p(_chk(dbias, torch.float32, "dbias")), B, C1, k, _stream()),
+          "conv1_valid_wgrad")
+
+
+def dropout_bf16(inp, out, rate: float, seed: int, step_ptr: Optional[torch.Tensor], layer_id: int):
+    check(lib().b200_dropout_bf16(_p(_chk(inp, bf16, "in")), _p(_chk(out, bf16, "out")), inp.numel(), float(rate),
+                                  ctypes.c_uint64(seed & (2 ** 64 - 1)), _p(step_ptr), layer_id, _stream()), "dropout_bf16")
 
 
 def maxpool_fwd(inp, out, argmax):
@@ -161,25 +182,26 @@ def gemm_tc_reduce_scatter(comm_handle, A, Bm, c_seg: int, c_off: int, nranks: i
           "gemm_tc_reduce_scatter")
 
 
-def conv_tc_fwd(inp, w, bias, out, argmax=None, *, relu=True, pool=False):
+def conv_tc_fwd(inp, w, bias, out, argmax=None, *, relu=True, pool=False, pad: Optional[int] = None):
+    """``pad=None``: SAME (k//2); ``pad=0``: VALID.  ``out`` is [B, H+2p-k+1, W+2p-k+1, Co] (halved when pooling)."""
     B, H, W, Ci = inp.shape
     k, Co = w.shape[0], w.shape[3]
-    check(lib().b200_conv_tc_fwd(_p(_chk(inp, bf16, "in")), _p(_chk(w, bf16, "w")), _p(bias), _p(_chk(out, bf16, "out")), _p(argmax),
-                                 B, H, W, Ci, Co, k, int(relu), int(pool), _stream()), "conv_tc_fwd")
+    check(lib().b200_conv_tc_fwd_pad(_p(_chk(inp, bf16, "in")), _p(_chk(w, bf16, "w")), _p(bias), _p(_chk(out, bf16, "out")), _p(argmax),
+                                     B, H, W, Ci, Co, k, k // 2 if pad is None else pad, int(relu), int(pool), _stream()), "conv_tc_fwd")
 
 
-def conv_tc_dgrad(dout, w, din):
+def conv_tc_dgrad(dout, w, din, *, pad: Optional[int] = None):
     B, H, W, Ci = din.shape
     k, Co = w.shape[0], w.shape[3]
-    check(lib().b200_conv_tc_dgrad(_p(_chk(dout, bf16, "dout")), _p(_chk(w, bf16, "w")), _p(_chk(din, bf16, "din")), _p(None),
-                                   B, H, W, Ci, Co, k, _stream()), "conv_tc_dgrad")
+    check(lib().b200_conv_tc_dgrad_pad(_p(_chk(dout, bf16, "dout")), _p(_chk(w, bf16, "w")), _p(_chk(din, bf16, "din")),
+                                       B, H, W, Ci, Co, k, k // 2 if pad is None else pad, _stream()), "conv_tc_dgrad")
 
 
-def conv_tc_wgrad(inp, dout, dw, dbias):
+def conv_tc_wgrad(inp, dout, dw, dbias, *, pad: Optional[int] = None):
     B, H, W, Ci = inp.shape
     k, Co = dw.shape[0], dw.shape[3]
-    check(lib().b200_conv_tc_wgrad(_p(_chk(inp, bf16, "in")), _p(_chk(dout, bf16, "dout")), _p(_chk(dw, torch.float32, "dw")), _p(dbias),
-                                   B, H, W, Ci, Co, k, _stream()), "conv_tc_wgrad")
+    check(lib().b200_conv_tc_wgrad_pad(_p(_chk(inp, bf16, "in")), _p(_chk(dout, bf16, "dout")), _p(_chk(dw, torch.float32, "dw")), _p(dbias),
+                                       B, H, W, Ci, Co, k, k // 2 if pad is None else pad, _stream()), "conv_tc_wgrad")
 
 
 def topology() -> dict:

@@ -189,9 +189,9 @@ def make_engine(spec: Optional[ModelSpec] = None, optimizer=None, *, engine: str
     use_cuda = torch.cuda.is_available() and (not _w.is_initialized() or _w.world().is_cuda)
     if engine == "auto":
         engine = "b200" if use_cuda else "torch"
-    if engine == "b200" and spec is not None and spec.arch != "mnist_cnn":
-        # the sm_100a engine implements the mnist_cnn family; other architectures (keras128) train through the
-        # PyTorch engine on the same device, with the same collectives underneath
+    if engine == "b200" and spec is not None and spec.arch not in ("mnist_cnn", "keras128"):
+        # architectures the sm_100a engine has no kernels for train through the PyTorch engine on the same device,
+        # with the same collectives underneath
         from ..utils.logging import get_logger
         get_logger().warning("engine_fallback", arch=spec.arch, engine="torch", device="cuda" if use_cuda else "cpu")
         kw.pop("batch_size", None); kw.pop("use_graph", None); kw.pop("use_tc", None)

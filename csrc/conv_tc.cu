@@ -1,8 +1,10 @@
-// Implicit-GEMM convolution on tcgen05 for sm_100a (NHWC bf16, stride 1, SAME padding, W <= 16).
+// Implicit-GEMM convolution on tcgen05 for sm_100a (NHWC bf16, stride 1, any padding 0..k-1: SAME and VALID).
 //
 // No im2col buffer exists anywhere: the filter taps are applied by the TMA unit — for tap (kh,kw) the
 // producer loads the SAME 4-D box {channels, 16, 8, 1} of the activation tensor shifted by (kh-pad, kw-pad),
-// and out-of-bounds rows/columns (the SAME halo, and columns W..15 of the 16-wide tile) arrive as zeros.
+// and out-of-bounds rows/columns (the SAME halo, and the part of a 16-wide tile past the image edge) arrive as zeros.
+// The source (TMA) tensor and the produced tensor may differ in size: a VALID forward reads HxW and writes
+// (H-k+1)x(W-k+1); its dgrad reads the small tensor and writes the big one ("full" correlation through OOB zeros).
 // An M tile is an 8x16 pixel patch of one image (row r = 16*hh + ww), so the 2x2 max-pool partners of a pixel
 // sit in the same warp's TMEM lanes (lane^1, lane^16, lane^17) and pooling is three shuffles in the epilogue.
 //
@@ -24,7 +26,7 @@ using namespace tc;
 constexpr int TILE_H = 8, TILE_W = 16, TILE_PIX = 128;
 
 struct ConvParams {
-  int B, H, W, Ci, Co, k, pad;
+  int B, Ho, Wo, Ci, Co, k, pad;      // Ho x Wo: spatial size of the tensor this launch PRODUCES
   int mode;          // 0 forward, 1 dgrad
   int KC;            // reduction channels per k-block (32 or 64)
   int BN;            // output channels per CTA
@@ -33,7 +35,7 @@ struct ConvParams {
   const bf16* bias;
   bf16* out;
   uint8_t* argmax;
-  int tiles_h;       // ceil(H / 8)
+  int tiles_h, tiles_w;       // ceil(Ho / 8), ceil(Wo / 16)
   uint32_t tmem_cols;
   int nstage;
 };
@@ -52,7 +54,9 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * p.BN;
-  const int img = blockIdx.y / p.tiles_h, h0 = (blockIdx.y % p.tiles_h) * TILE_H;
+  const int tiles_hw = p.tiles_h * p.tiles_w;
+  const int img = blockIdx.y / tiles_hw, tile = blockIdx.y % tiles_hw;
+  const int h0 = (tile / p.tiles_w) * TILE_H, w0 = (tile % p.tiles_w) * TILE_W;
   const int nkb = p.k * p.k * p.kc_blocks;
   const uint32_t swz = p.KC == 64 ? SW_128B : SW_64B;
   const int row_bytes = p.KC * 2;
@@ -85,7 +89,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         uint8_t* sA = smem + stage * stage_bytes;
         uint8_t* sB = sA + a_bytes;
         mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + b_bytes));
-        tma_load_4d(sA, &tmA, full + stage, cb * p.KC, dw, h0 + dh, img);
+        tma_load_4d(sA, &tmA, full + stage, cb * p.KC, w0 + dw, h0 + dh, img);
         if (p.mode == 0) {
           // rows = (tap, ci) block, cols = co: MN-major B, one 64-column box per 64 output channels
           for (int j = 0; j < p.BN / 64; ++j)
@@ -126,7 +130,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
     mbar_wait(tmem_full, 0, 13);
     tc_fence_after();
     const int q = warp & 3;
-    const int hh = 2 * q + (lane >> 4), ww = lane & 15;
+    const int hh = 2 * q + (lane >> 4), ww = w0 + (lane & 15);
     const int h = h0 + hh;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     const int Cout = p.mode == 0 ? p.Co : p.Ci;
@@ -158,14 +162,14 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
           if (j & 1) packed[j >> 1] |= hb << 16; else packed[j >> 1] = hb;
           am[j >> 2] |= bi << (8 * (j & 3));
         }
-        if (lane < 16 && !(lane & 1) && ww < p.W && h < p.H) {
-          const size_t o = (((size_t)img * (p.H / 2) + h / 2) * (p.W / 2) + ww / 2) * Cout + n0 + c;
+        if (lane < 16 && !(lane & 1) && ww < p.Wo && h < p.Ho) {
+          const size_t o = (((size_t)img * (p.Ho / 2) + h / 2) * (p.Wo / 2) + ww / 2) * Cout + n0 + c;
           *reinterpret_cast<uint4*>(p.out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
           *reinterpret_cast<uint4*>(p.out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
           if (p.argmax) *reinterpret_cast<uint4*>(p.argmax + o) = make_uint4(am[0], am[1], am[2], am[3]);
         }
-      } else if (ww < p.W && h < p.H) {
-        const size_t o = (((size_t)img * p.H + h) * p.W + ww) * Cout + n0 + c;
+      } else if (ww < p.Wo && h < p.Ho) {
+        const size_t o = (((size_t)img * p.Ho + h) * p.Wo + ww) * Cout + n0 + c;
         uint2 lo = pack_bf16x4(make_float4(v[0], v[1], v[2], v[3])), l2 = pack_bf16x4(make_float4(v[4], v[5], v[6], v[7]));
         uint2 hi = pack_bf16x4(make_float4(v[8], v[9], v[10], v[11])), h2 = pack_bf16x4(make_float4(v[12], v[13], v[14], v[15]));
         *reinterpret_cast<uint4*>(p.out + o) = make_uint4(lo.x, lo.y, l2.x, l2.y);
@@ -182,13 +186,13 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
 // wgrad: M tile = G stacked (tap, channel-block) pairs, G*CB = 128; K = pixels.
 // ------------------------------------------------------------------------------------------------
 struct WgradParams {
-  int B, H, W, Ci, Co, k, pad;
+  int B, Ci, Co, k, pad;
   int CB;            // channels per A box: 32 (64-byte rows) or 64 (128-byte rows)
   int G;             // pairs per M tile = 128 / CB
   int cblocks;       // Ci / CB
   int npairs;        // k*k*cblocks
   int BN;
-  int tiles_h, ntiles, tiles_per_split;
+  int tiles_h, tiles_w, ntiles, tiles_per_split;   // pixel tiles run over the dy tensor (Ho x Wo)
   float* dw;
   uint32_t tmem_cols;
   int nstage;
@@ -234,7 +238,9 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_cons
     int stage = 0;
     uint32_t phase = 0;
     for (int t = t0; t < t1; ++t) {
-      const int img = t / p.tiles_h, h0 = (t % p.tiles_h) * TILE_H;
+      const int tiles_hw = p.tiles_h * p.tiles_w;
+      const int img = t / tiles_hw, tile = t % tiles_hw;
+      const int h0 = (tile / p.tiles_w) * TILE_H, w0 = (tile % p.tiles_w) * TILE_W;
       mbar_wait(empty + stage, phase ^ 1, 21);
       if (leader) {
         uint8_t* sA = smem + stage * stage_bytes;
@@ -244,9 +250,9 @@ __global__ void __launch_bounds__(192, 1) conv_wgrad_tc_kernel(const __grid_cons
           const int pr = pair0 + j;
           const int tap = pr / p.cblocks, cb = pr % p.cblocks;
           const int kh = tap / p.k, kw = tap % p.k;
-          tma_load_4d(sA + j * box_bytes, &tmIn, full + stage, cb * p.CB, kw - p.pad, h0 + kh - p.pad, img);
+          tma_load_4d(sA + j * box_bytes, &tmIn, full + stage, cb * p.CB, w0 + kw - p.pad, h0 + kh - p.pad, img);
         }
-        for (int j = 0; j < p.BN / 64; ++j) tma_load_4d(sB + j * (TILE_PIX * 128), &tmDy, full + stage, n0 + 64 * j, 0, h0, img);
+        for (int j = 0; j < p.BN / 64; ++j) tma_load_4d(sB + j * (TILE_PIX * 128), &tmDy, full + stage, n0 + 64 * j, w0, h0, img);
       }
       __syncwarp();
       if (++stage == p.nstage) { stage = 0; phase ^= 1; }
@@ -327,16 +333,20 @@ int set_smem(const void* fn) {
   return B200_OK;
 }
 
+// H x W is the spatial size of the forward INPUT; the forward output (= dgrad input) is Hf x Wf = H+2*pad-k+1.
 int launch_conv(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W,
-                int Ci, int Co, int k, int relu, int pool, cudaStream_t st) {
+                int Ci, int Co, int k, int pad, int relu, int pool, cudaStream_t st) {
   const int Cred = mode == 0 ? Ci : Co;      // reduction channels
   const int Cout = mode == 0 ? Co : Ci;      // channels produced
-  B200_REQUIRE(W <= TILE_W && W >= 1 && H >= 1, "conv_tc: W=%d must be <= 16", W);
-  B200_REQUIRE(k % 2 == 1 && k <= 7, "conv_tc: odd kernel size <= 7 expected, got %d", k);
+  B200_REQUIRE(k >= 1 && k <= 7 && pad >= 0 && pad < k, "conv_tc: kernel size %d (<= 7) / padding %d (< k) unsupported", k, pad);
+  const int Hf = H + 2 * pad - k + 1, Wf = W + 2 * pad - k + 1;
+  B200_REQUIRE(W >= 1 && H >= 1 && Hf >= 1 && Wf >= 1, "conv_tc: empty tensor (%dx%d -> %dx%d)", H, W, Hf, Wf);
   B200_REQUIRE(Cred % 32 == 0, "conv_tc: reduction channels %d must be a multiple of 32", Cred);
-  B200_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "conv_tc: pooling needs even H, W");
+  const int Hs = mode == 0 ? H : Hf, Ws = mode == 0 ? W : Wf;       // tensor the TMA reads
+  const int Ho = mode == 0 ? Hf : H, Wo = mode == 0 ? Wf : W;       // tensor this launch writes
+  B200_REQUIRE(!pool || (Ho % 2 == 0 && Wo % 2 == 0), "conv_tc: pooling needs an even output size, got %dx%d", Ho, Wo);
   ConvParams p;
-  p.B = B; p.H = H; p.W = W; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = k / 2; p.mode = mode;
+  p.B = B; p.Ho = Ho; p.Wo = Wo; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = pad; p.mode = mode;
   p.KC = Cred % 64 == 0 ? 64 : 32;
   p.kc_blocks = Cred / p.KC;
   if (mode == 0) {
@@ -347,7 +357,8 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
     p.BN = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
   }
   p.relu = relu; p.pool = pool; p.bias = (const bf16*)bias; p.out = (bf16*)out; p.argmax = argmax;
-  p.tiles_h = (H + TILE_H - 1) / TILE_H;
+  p.tiles_h = (Ho + TILE_H - 1) / TILE_H;
+  p.tiles_w = (Wo + TILE_W - 1) / TILE_W;
   uint32_t cols = 32;
   while ((int)cols < p.BN) cols <<= 1;
   p.tmem_cols = cols;
@@ -359,7 +370,7 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
 
   CUtensorMap tmA, tmB;
   int rc;
-  if ((rc = act_tmap(&tmA, act, B, H, W, Cred, p.KC))) return rc;
+  if ((rc = act_tmap(&tmA, act, B, Hs, Ws, Cred, p.KC))) return rc;
   {
     const uint64_t dims[2] = {(uint64_t)Co, (uint64_t)k * k * Ci}, str[1] = {(uint64_t)Co * 2};
     if (mode == 0) {
@@ -372,7 +383,7 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
   }
   static bool attr = false;
   if (!attr) { if ((rc = set_smem((const void*)conv_tc_kernel))) return rc; attr = true; }
-  dim3 grid(Cout / p.BN, B * p.tiles_h);
+  dim3 grid(Cout / p.BN, B * p.tiles_h * p.tiles_w);
   B200_CHECK(launch_pdl(conv_tc_kernel, grid, dim3(192), smem, st, tmA, tmB, p));
   return B200_OK;
 }
@@ -389,40 +400,55 @@ static bool halo_enabled() {
 
 extern "C" {
 
-int b200_conv_tc_fwd(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W, int Ci,
-                     int Co, int k, int relu, int pool, void* stream) {
-  if (halo_enabled()) {
+int b200_conv_tc_fwd_pad(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W,
+                         int Ci, int Co, int k, int pad, int relu, int pool, void* stream) {
+  if (halo_enabled() && pad == k / 2 && (k & 1)) {
     const int rc = b200_conv_halo_launch(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
     if (rc != B200_ERR_UNSUPPORTED) return rc;
   }
-  return launch_conv(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
+  return launch_conv(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, pad, relu, pool, (cudaStream_t)stream);
+}
+
+int b200_conv_tc_fwd(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W, int Ci,
+                     int Co, int k, int relu, int pool, void* stream) {
+  B200_REQUIRE(k % 2 == 1, "conv_tc: SAME padding needs an odd kernel size, got %d", k);
+  return b200_conv_tc_fwd_pad(in, w, bias, out, argmax, B, H, W, Ci, Co, k, k / 2, relu, pool, stream);
+}
+
+int b200_conv_tc_dgrad_pad(const void* dout, const void* w, void* din, int B, int H, int W, int Ci, int Co, int k, int pad,
+                           void* stream) {
+  if (halo_enabled() && pad == k / 2 && (k & 1)) {
+    const int rc = b200_conv_halo_launch(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  return launch_conv(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, pad, 0, 0, (cudaStream_t)stream);
 }
 
 int b200_conv_tc_dgrad(const void* dout, const void* w, void* din, const void* mask_src, int B, int H, int W, int Ci, int Co,
                        int k, void* stream) {
   (void)mask_src;
-  if (halo_enabled()) {
-    const int rc = b200_conv_halo_launch(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
-    if (rc != B200_ERR_UNSUPPORTED) return rc;
-  }
-  return launch_conv(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
+  B200_REQUIRE(k % 2 == 1, "conv_tc: SAME padding needs an odd kernel size, got %d", k);
+  return b200_conv_tc_dgrad_pad(dout, w, din, B, H, W, Ci, Co, k, k / 2, stream);
 }
 
-int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co, int k,
-                       void* stream) {
-  B200_REQUIRE(W <= TILE_W, "conv_tc wgrad: W=%d must be <= 16", W);
+int b200_conv_tc_wgrad_pad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co,
+                           int k, int pad, void* stream) {
+  B200_REQUIRE(k >= 1 && k <= 7 && pad >= 0 && pad < k, "conv_tc wgrad: kernel size %d / padding %d unsupported", k, pad);
+  const int Ho = H + 2 * pad - k + 1, Wo = W + 2 * pad - k + 1;
+  B200_REQUIRE(Ho >= 1 && Wo >= 1, "conv_tc wgrad: empty output");
   B200_REQUIRE(Ci % 32 == 0 && (Ci == 32 || Ci % 64 == 0), "conv_tc wgrad: Ci=%d must be 32 or a multiple of 64", Ci);
   B200_REQUIRE(Co % 64 == 0, "conv_tc wgrad: Co=%d must be a multiple of 64", Co);
   cudaStream_t st = (cudaStream_t)stream;
   WgradParams p;
-  p.B = B; p.H = H; p.W = W; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = k / 2;
+  p.B = B; p.Ci = Ci; p.Co = Co; p.k = k; p.pad = pad;
   p.CB = Ci == 32 ? 32 : 64;
   p.G = 128 / p.CB;
   p.cblocks = Ci / p.CB;
   p.npairs = k * k * p.cblocks;
   p.BN = Co % 128 == 0 ? 128 : 64;
-  p.tiles_h = (H + TILE_H - 1) / TILE_H;
-  p.ntiles = B * p.tiles_h;
+  p.tiles_h = (Ho + TILE_H - 1) / TILE_H;
+  p.tiles_w = (Wo + TILE_W - 1) / TILE_W;
+  p.ntiles = B * p.tiles_h * p.tiles_w;
   p.dw = dw;
   uint32_t cols = 32;
   while ((int)cols < p.BN) cols <<= 1;
@@ -440,15 +466,21 @@ int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias
   CUtensorMap tmIn, tmDy;
   int rc;
   if ((rc = act_tmap(&tmIn, in, B, H, W, Ci, p.CB))) return rc;
-  if ((rc = act_tmap(&tmDy, dout, B, H, W, Co, 64))) return rc;
+  if ((rc = act_tmap(&tmDy, dout, B, Ho, Wo, Co, 64))) return rc;
   static bool attr = false;
   if (!attr) { if ((rc = set_smem((const void*)conv_wgrad_tc_kernel))) return rc; attr = true; }
   B200_CHECK(launch_pdl(conv_wgrad_tc_kernel, dim3(mtiles, ntile_n, split), dim3(192), smem, st, tmIn, tmDy, p));
   if (dbias) {
-    colsum_bf16_kernel<<<148, Co < 256 ? (Co + 31) / 32 * 32 : 256, 0, st>>>((const bf16*)dout, dbias, (long long)B * H * W, Co);
+    colsum_bf16_kernel<<<148, Co < 256 ? (Co + 31) / 32 * 32 : 256, 0, st>>>((const bf16*)dout, dbias, (long long)B * Ho * Wo, Co);
     B200_LAUNCH_CHECK();
   }
   return B200_OK;
+}
+
+int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co, int k,
+                       void* stream) {
+  B200_REQUIRE(k % 2 == 1, "conv_tc: SAME padding needs an odd kernel size, got %d", k);
+  return b200_conv_tc_wgrad_pad(in, dout, dw, dbias, B, H, W, Ci, Co, k, k / 2, stream);
 }
 
 }  // extern "C"

@@ -138,6 +138,137 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------------------------------------
+// keras128 first layer: KxK VALID, Cin=1 -> C1, + bias + ReLU (no pooling), NHWC bf16 out.
+// Lane = output channel (taps in registers), the image in shared memory; blockIdx.y splits the pixels.
+// Keras: Conv2D(32, (3,3), activation='relu') — the shape BASELINE.json's prose names.
+// ------------------------------------------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(256) conv1_valid_fwd_kernel(const float* __restrict__ x, const bf16* __restrict__ w,
+                                                              const bf16* __restrict__ bias, bf16* __restrict__ out, int C1,
+                                                              int* step_ptr, int bump_step, float* loss_ring,
+                                                              int* correct_ring, int ring) {
+  constexpr int HO = 28 - K + 1, NPIX = HO * HO;
+  __shared__ float img[28][29];
+  const int b = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
+  if (bump_step && b == 0 && blockIdx.y == 0 && threadIdx.x == 0 && step_ptr) {
+    const int s = *step_ptr + 1;
+    *step_ptr = s;
+    if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+  }
+  for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int per = (NPIX + gridDim.y - 1) / gridDim.y;
+  const int p0 = blockIdx.y * per, p1 = min(NPIX, p0 + per);
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + lane;
+    float wr[K * K];
+#pragma unroll
+    for (int t = 0; t < K * K; ++t) wr[t] = c < C1 ? bf(w + t * C1 + c) : 0.f;
+    const float bb = c < C1 ? bf(bias + c) : 0.f;
+    for (int p = p0 + warp; p < p1; p += nwarp) {
+      const int y = p / HO, xq = p % HO;
+      float acc = bb;
+#pragma unroll
+      for (int kh = 0; kh < K; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < K; ++kw) acc = fmaf(img[y + kh][xq + kw], wr[kh * K + kw], acc);
+      if (c < C1) out[((size_t)b * NPIX + p) * C1 + c] = __float2bfloat16(fmaxf(acc, 0.f));
+    }
+  }
+}
+
+// dW[tap,c] = sum_{b,pix} x[b, pix+tap] * da1[b,pix,c] * (a1 > 0);  dbias[c] = the same sum without x.
+template <int K>
+__global__ void __launch_bounds__(256) conv1_valid_wgrad_kernel(const float* __restrict__ x, const bf16* __restrict__ da1,
+                                                                const bf16* __restrict__ a1, float* __restrict__ dw,
+                                                                float* __restrict__ dbias, int B, int C1) {
+  constexpr int HO = 28 - K + 1, NPIX = HO * HO, NT = K * K + 1;
+  __shared__ float img[28][29];
+  __shared__ float red[8][NT][32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int per = (NPIX + gridDim.y - 1) / gridDim.y;
+  const int p0 = blockIdx.y * per, p1 = min(NPIX, p0 + per);
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + lane;
+    float acc[NT];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) acc[t] = 0.f;
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
+      __syncthreads();
+      if (c < C1) {
+        for (int pb = p0 + warp; pb < p1; pb += 4 * nwarp) {
+          // four pixels per trip: their loads are in flight together
+          float gv[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int p = pb + i * nwarp;
+            gv[i] = 0.f;
+            if (p < p1) {
+              const size_t o = ((size_t)b * NPIX + p) * C1 + c;
+              gv[i] = bf(a1 + o) > 0.f ? bf(da1 + o) : 0.f;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int p = pb + i * nwarp;
+            if (p >= p1) continue;
+            const int y = p / HO, xq = p % HO;
+            const float g = gv[i];
+#pragma unroll
+            for (int kh = 0; kh < K; ++kh)
+#pragma unroll
+              for (int kw = 0; kw < K; ++kw) acc[kh * K + kw] = fmaf(img[y + kh][xq + kw], g, acc[kh * K + kw]);
+            acc[K * K] += g;
+          }
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < NT; ++t) red[warp][t][lane] = acc[t];
+    __syncthreads();
+    for (int i = threadIdx.x; i < NT * 32; i += blockDim.x) {
+      const int t = i >> 5, l = i & 31;
+      float s = 0.f;
+      for (int wv = 0; wv < nwarp; ++wv) s += red[wv][t][l];
+      if (c0 + l < C1) {
+        if (t < K * K) atomicAdd(dw + t * C1 + c0 + l, s);
+        else atomicAdd(dbias + c0 + l, s);
+      }
+    }
+  }
+}
+
+// Inverted dropout over a bf16 tensor (in place allowed): element i keeps its value * 1/(1-rate) when Philox lane i%4 of
+// counter (i/4, 0, step, layer) is >= rate * 2^32 — the same stream b200dp/utils/philox.py draws on the host.
+__global__ void __launch_bounds__(256) dropout_bf16_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, long long n4,
+                                                           float rate, uint64_t seed, const int* step_ptr, int layer_id) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const uint32_t step = step_ptr ? (uint32_t)*step_ptr : 0u;
+  const uint32_t thresh = (uint32_t)fminf(rate * 4294967296.f, 4294967295.f);
+  const float sc = 1.f / (1.f - rate);
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (long long)gridDim.x * blockDim.x) {
+    const uint4 rnd = dropout_rand4((uint32_t)q, step, (uint32_t)layer_id, seed);
+    const uint2 raw = *reinterpret_cast<const uint2*>(in + 4 * q);
+    const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&raw.x), hi = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+    float4 v = make_float4(__low2float(lo), __high2float(lo), __low2float(hi), __high2float(hi));
+    v.x = rnd.x >= thresh ? v.x * sc : 0.f;
+    v.y = rnd.y >= thresh ? v.y * sc : 0.f;
+    v.z = rnd.z >= thresh ? v.z * sc : 0.f;
+    v.w = rnd.w >= thresh ? v.w * sc : 0.f;
+    *reinterpret_cast<uint2*>(out + 4 * q) = pack_bf16x4(v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Classifier head, one batch row per block:
 //   h = dropout(relu(z + b1));  logits = h W2 + b2;  loss/acc;  dlogits = (softmax - onehot)/B;
 //   dz = (dlogits W2^T) * relu'/dropout mask.   z is cleared afterwards (split-K accumulator).
@@ -298,7 +429,8 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const bf16* __restrict_
 // gradient (sum of dy over batch and space) accumulates in a register and costs one atomic per thread group.
 __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const bf16* __restrict__ dpool, const bf16* __restrict__ pooled,
                                                               const uint8_t* __restrict__ argmax, bf16* __restrict__ dy,
-                                                              float* __restrict__ dbias, int HP, int WP, int C, long long total) {
+                                                              float* __restrict__ dbias, int HP, int WP, int C, long long total,
+                                                              float gscale) {
   __shared__ float red[256];
   pdl_wait();
   pdl_launch_dependents();
@@ -310,7 +442,7 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const bf16* __rest
     const int pw = (int)(p % WP); p /= WP;
     const int ph = (int)(p % HP);
     const long long b = p / HP;
-    const float g = bf(pooled + i) > 0.f ? bf(dpool + i) : 0.f;
+    const float g = bf(pooled + i) > 0.f ? bf(dpool + i) * gscale : 0.f;
     bsum += g;
     const int q = argmax[i];
     const int W = 2 * WP;
@@ -592,8 +724,10 @@ int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* 
   return B200_OK;
 }
 
-int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, float* dbias, int B, int HP,
-                         int WP, int C, void* stream) {
+// `pooled` may be the tensor AFTER an inverted dropout of keep-scale `gscale` (keras128): a dropped or ReLU-clamped element
+// is 0 there and passes no gradient, a kept one passes dpool * gscale.
+int b200_unpool_relu_bwd_scaled(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, float* dbias, int B,
+                                int HP, int WP, int C, float gscale, void* stream) {
   const long long total = (long long)B * HP * WP * C;
   int grid = grid_for(total, 256, 148 * 4);
   if (dbias && 256 % C != 0) {
@@ -602,7 +736,42 @@ int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* a
     B200_REQUIRE((256LL * grid) % C == 0, "unpool: cannot build a channel-stable stride for C=%d", C);
   }
   B200_CHECK(launch_pdl(unpool_relu_bwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const bf16*)dpool, (const bf16*)pooled,
-                        argmax, (bf16*)dy, dbias, HP, WP, C, total));
+                        argmax, (bf16*)dy, dbias, HP, WP, C, total, gscale));
+  return B200_OK;
+}
+
+int b200_unpool_relu_bwd(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, float* dbias, int B, int HP,
+                         int WP, int C, void* stream) {
+  return b200_unpool_relu_bwd_scaled(dpool, pooled, argmax, dy, dbias, B, HP, WP, C, 1.f, stream);
+}
+
+int b200_conv1_valid_fwd(const float* x, const void* w, const void* bias, void* out, int B, int C1, int k, int* step_ptr,
+                         int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream) {
+  B200_REQUIRE(B > 0 && C1 > 0, "conv1_valid: bad shape B=%d C1=%d", B, C1);
+  B200_REQUIRE(k == 3 || k == 5, "conv1_valid: kernel size %d not instantiated (3 or 5)", k);
+  auto kern = k == 3 ? conv1_valid_fwd_kernel<3> : conv1_valid_fwd_kernel<5>;
+  B200_CHECK(launch_pdl(kern, dim3(B, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)w, (const bf16*)bias, (bf16*)out, C1,
+                        step_ptr, bump_step, loss_ring, correct_ring, ring));
+  return B200_OK;
+}
+
+int b200_conv1_valid_wgrad(const float* x, const void* da1, const void* a1, float* dw, float* dbias, int B, int C1, int k,
+                           void* stream) {
+  B200_REQUIRE(B > 0 && C1 > 0, "conv1_valid wgrad: bad shape");
+  B200_REQUIRE(k == 3 || k == 5, "conv1_valid wgrad: kernel size %d not instantiated (3 or 5)", k);
+  auto kern = k == 3 ? conv1_valid_wgrad_kernel<3> : conv1_valid_wgrad_kernel<5>;
+  const int grid = B < 74 ? B : 74;
+  B200_CHECK(launch_pdl(kern, dim3(grid, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)da1, (const bf16*)a1, dw, dbias, B, C1));
+  return B200_OK;
+}
+
+int b200_dropout_bf16(const void* in, void* out, long long n, float rate, uint64_t seed, const int* step_ptr, int layer_id,
+                      void* stream) {
+  B200_REQUIRE(n > 0 && n % 4 == 0, "dropout: element count %lld must be a positive multiple of 4", n);
+  B200_REQUIRE(rate >= 0.f && rate < 1.f, "dropout: rate %f outside [0,1)", rate);
+  B200_REQUIRE((n >> 2) <= 0xFFFFFFFFLL, "dropout: tensor too large for a 32-bit Philox counter");
+  B200_CHECK(launch_pdl(dropout_bf16_kernel, dim3(grid_for(n / 4, 256, 148 * 8)), dim3(256), 0, (cudaStream_t)stream, (const bf16*)in,
+                        (bf16*)out, n / 4, rate, seed, step_ptr, layer_id));
   return B200_OK;
 }
 

@@ -110,6 +110,21 @@ int b200_head_wgrad(const void* h_bf16, const void* dz_bf16, const float* dlogit
 int b200_unpool_relu_bwd(const void* dpool_bf16, const void* pooled_bf16, const uint8_t* argmax, void* dy_bf16,
                          float* dbias, int B, int HP, int WP, int C, void* stream);
 int b200_maxpool_fwd(const void* in_bf16, void* out_bf16, uint8_t* argmax, int B, int H, int W, int C, void* stream);
+/* same, when `pooled` is the tensor after an inverted dropout of keep-scale gscale = 1/(1-rate) (Keras: MaxPooling2D ->
+ * Dropout(0.25)): zero entries (ReLU-clamped or dropped) pass nothing, the rest pass dpool * gscale */
+int b200_unpool_relu_bwd_scaled(const void* dpool_bf16, const void* pooled_bf16, const uint8_t* argmax, void* dy_bf16,
+                                float* dbias, int B, int HP, int WP, int C, float gscale, void* stream);
+/* keras128 first layer: k x k VALID conv (k = 3 or 5), Cin=1 -> C1, + bias + ReLU, out [B,28-k+1,28-k+1,C1] bf16.
+ * step_ptr / ring: as b200_conv1_pool_fwd. */
+int b200_conv1_valid_fwd(const float* x, const void* w_bf16, const void* bias_bf16, void* out_bf16, int B, int C1, int k,
+                         int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream);
+/* its weight/bias gradient (accumulates): dW[tap,c] += sum x[pix+tap] * da1[pix,c] * (a1[pix,c] > 0) */
+int b200_conv1_valid_wgrad(const float* x, const void* da1_bf16, const void* a1_bf16, float* dw, float* dbias, int B,
+                           int C1, int k, void* stream);
+/* inverted dropout on a bf16 tensor of n (multiple of 4) elements, in place allowed; Philox4x32-10 keyed by
+ * (seed, *step_ptr, layer_id), the stream b200dp/utils/philox.py reproduces on the host */
+int b200_dropout_bf16(const void* in_bf16, void* out_bf16, long long n, float rate, uint64_t seed, const int* step_ptr,
+                      int layer_id, void* stream);
 /* direct convolution fallbacks (any k, stride 1), NHWC bf16, fp32 accumulate */
 int b200_conv_direct_fwd(const void* in, const void* w, const void* bias, void* out, int B, int H, int W, int Ci,
                          int Co, int k, int pad, int relu, void* stream);
@@ -150,6 +165,15 @@ int b200_conv_tc_dgrad(const void* dout, const void* w, void* din, const void* m
                        int Co, int k, void* stream);
 int b200_conv_tc_wgrad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci, int Co,
                        int k, void* stream);
+/* The same three kernels with an explicit padding 0 <= pad < k (pad = 0: VALID) and any spatial size (the pixel tiles
+ * walk W as well as H).  H x W is always the forward INPUT size; the forward output / dout is
+ * (H+2*pad-k+1) x (W+2*pad-k+1). */
+int b200_conv_tc_fwd_pad(const void* in, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H, int W,
+                         int Ci, int Co, int k, int pad, int relu, int pool, void* stream);
+int b200_conv_tc_dgrad_pad(const void* dout, const void* w, void* din, int B, int H, int W, int Ci, int Co, int k,
+                           int pad, void* stream);
+int b200_conv_tc_wgrad_pad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci,
+                           int Co, int k, int pad, void* stream);
 
 /* ---- host runtime ---- */
 /* JSON description of the visible GPUs: names, SM counts, memory, peer-access matrix. Returns bytes written. */

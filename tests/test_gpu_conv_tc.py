@@ -69,3 +69,46 @@ def test_conv_tc_dgrad_wgrad(B, H, Ci, Co, k):
     assert e <= 5e-3 * s + 1e-2, f"wgrad: err {e} scale {s}"
     e, s = _err(db, dy.float().sum((0, 1, 2)))
     assert e <= 1e-3 * s + 1e-2
+
+
+# ---- explicit padding (VALID) and images wider than one 16-pixel tile: the keras128 second layer and friends ----
+@pytest.mark.parametrize("B,H,Ci,Co,k,pad", [(2, 26, 32, 64, 3, 0), (128, 26, 32, 64, 3, 0), (3, 20, 64, 128, 5, 0),
+                                             (2, 28, 32, 64, 3, 1), (5, 18, 32, 64, 3, 2)])
+def test_conv_tc_padded_fwd(B, H, Ci, Co, k, pad):
+    x, w, b, xr, wr = _setup(B, H, Ci, Co, k, 5)
+    Ho = H + 2 * pad - k + 1
+    pre = F.relu(F.conv2d(xr, wr, b.float(), padding=pad))
+    out = torch.full((B, Ho, Ho, Co), float("nan"), device="cuda", dtype=bf16)
+    K.conv_tc_fwd(x, w, b, out, None, relu=True, pool=False, pad=pad)
+    e, s = _err(out, pre.permute(0, 2, 3, 1))
+    assert e <= 2e-2 * s + 2e-2, f"unpooled: err {e} scale {s}"
+    if Ho % 2 == 0:
+        pooled = torch.full((B, Ho // 2, Ho // 2, Co), float("nan"), device="cuda", dtype=bf16)
+        am = torch.full((B, Ho // 2, Ho // 2, Co), 255, device="cuda", dtype=torch.uint8)
+        K.conv_tc_fwd(x, w, b, pooled, am, relu=True, pool=True, pad=pad)
+        e, s = _err(pooled, F.max_pool2d(pre, 2).permute(0, 2, 3, 1))
+        assert e <= 2e-2 * s + 2e-2, f"pooled: err {e} scale {s}"
+        win = out.float().view(B, Ho // 2, 2, Ho // 2, 2, Co).permute(0, 1, 3, 5, 2, 4).reshape(B, Ho // 2, Ho // 2, Co, 4)
+        picked = torch.gather(win, 4, am.long().unsqueeze(-1)).squeeze(-1)
+        assert torch.equal(picked, pooled.float())
+
+
+@pytest.mark.parametrize("B,H,Ci,Co,k,pad", [(2, 26, 32, 64, 3, 0), (128, 26, 32, 64, 3, 0), (3, 20, 64, 128, 5, 0),
+                                             (2, 28, 32, 64, 3, 1), (5, 18, 32, 64, 3, 2)])
+def test_conv_tc_padded_dgrad_wgrad(B, H, Ci, Co, k, pad):
+    x, w, b, xr, wr = _setup(B, H, Ci, Co, k, 6)
+    Ho = H + 2 * pad - k + 1
+    dy = torch.randn(B, Ho, Ho, Co, device="cuda").to(bf16)
+    F.conv2d(xr, wr, None, padding=pad).backward(dy.float().permute(0, 3, 1, 2))
+    din = torch.full((B, H, H, Ci), float("nan"), device="cuda", dtype=bf16)
+    K.conv_tc_dgrad(dy, w, din, pad=pad)
+    e, s = _err(din, xr.grad.permute(0, 2, 3, 1))
+    assert e <= 2e-2 * s + 2e-2, f"dgrad: err {e} scale {s}"
+    dw = torch.zeros(k, k, Ci, Co, device="cuda")
+    db = torch.zeros(Co, device="cuda")
+    K.conv_tc_wgrad(x, dy, dw, db, pad=pad)
+    ref = wr.grad.permute(2, 3, 1, 0)
+    e, s = _err(dw, ref)
+    assert e <= 1e-2 * s + 1e-2, f"wgrad: err {e} scale {s}"
+    e, s = _err(db, dy.float().sum((0, 1, 2)))
+    assert e <= 1e-2 * s + 1e-2, f"dbias: err {e} scale {s}"

@@ -95,3 +95,65 @@ def test_keras_front_end_on_gpu(data):
                   callbacks=[hvd.callbacks.BroadcastGlobalVariablesCallback(0), hvd.callbacks.MetricAverageCallback()], verbose=0)
     assert h.history["loss"][1] < h.history["loss"][0]
     assert 0 <= h.history["val_accuracy"][-1] <= 1
+
+
+# ---- keras128 (conv3x3x32 -> conv3x3x64 -> pool -> dropout -> dense128 -> dropout -> dense10) on the same engine ----
+def _kpair(B, dropout, use_tc=True, use_graph=False, width=1.0, lr=1e-3):
+    spec = hvd.get_spec("keras128", width)
+    opt = hvd.DistributedOptimizer(hvd.Adam.keras(lr))
+    g = B200Engine(spec, opt, seed=5, batch_size=B, dropout=dropout, use_tc=use_tc, use_graph=use_graph)
+    c = TorchEngine(spec, opt, seed=5, device="cuda", dropout=dropout, compute_dtype=torch.bfloat16)
+    return g, c
+
+
+@pytest.mark.parametrize("use_tc", [False, True])
+@pytest.mark.parametrize("B,dropout", [(128, False), (100, True), (32, True)])
+def test_keras128_steps_match_oracle(data, B, dropout, use_tc):
+    x, y, _, _ = data
+    g, c = _kpair(B, dropout, use_tc)
+    assert g.keras and g.tc_conv == use_tc and g.F == 9216 and g.D == 128
+    for s in range(3):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        rg, rc = g.train_step(xb, yb), c.train_step(xb, yb)
+        assert abs(rg.loss_value() - rc.loss_value()) < 3e-2 * max(1.0, abs(rc.loss_value())), (s, rg.loss_value(), rc.loss_value())
+        assert abs(int(rg.correct) - int(rc.correct)) <= max(2, B // 20)
+    torch.cuda.synchronize()
+    from b200dp.models.spec import init_flat
+    init = init_flat(g.spec, 5, "cuda")
+    for p in g.spec.params:
+        dg = (g.master - init)[p.offset:p.offset + p.numel]
+        dc = (c.params.data - init)[p.offset:p.offset + p.numel]
+        cos = torch.nn.functional.cosine_similarity(dg, dc, dim=0).item()
+        assert cos > 0.9, f"{p.name}: update direction cosine {cos}"
+    # inference path (no dropout kernels) against the oracle
+    lg, lc = g.predict(x[:B]), c.predict(x[:B])
+    assert (lg - lc).abs().max().item() < 5e-2 * max(1.0, lc.abs().max().item())
+
+
+def test_keras128_trains_from_graph_and_roundtrips(data, tmp_path):
+    x, y, xt, yt = data
+    B = 128
+    g, _ = _kpair(B, True, use_graph=True, lr=2e-3)
+    first = g.train_step(x[:B], y[:B]).loss_value()
+    for it in range(60):
+        i = (it % 8) * B
+        last = g.train_step(x[i:i + B], y[i:i + B])
+    assert last.loss_value() < 0.5 * first
+    assert len(g._graphs) == 2 and g.launches_per_step >= 10
+    ev = g.eval_batch(xt, yt)
+    assert ev.accuracy() > 0.8 and np.isfinite(ev.loss_value())
+    st = g.state()
+    nxt = g.train_step(x[:B], y[:B]).loss_value()
+    h, _ = _kpair(B, True, use_graph=True, lr=2e-3)
+    h.load_state(st["tensors"], st["meta"])
+    assert abs(h.train_step(x[:B], y[:B]).loss_value() - nxt) < 1e-3 * max(1.0, abs(nxt))
+
+
+def test_keras128_through_model_api(data):
+    x, y, xt, yt = data
+    m = hvd.Model(hvd.get_spec("keras128"), seed=2, batch_size=64)
+    m.compile(optimizer=hvd.DistributedOptimizer(hvd.Adam.keras(2e-3)), loss=hvd.SparseCategoricalCrossentropy(from_logits=True),
+              metrics=["accuracy"])
+    hist = m.fit(x, y, batch_size=64, epochs=2, verbose=0)
+    assert type(m.engine).__name__ == "B200Engine" and m.engine.keras
+    assert hist.history["loss"][-1] < hist.history["loss"][0]

@@ -180,3 +180,68 @@ def test_topology_reports_devices():
     t = K.topology()
     assert len(t["gpus"]) == torch.cuda.device_count() and t["gpus"][0]["sms"] > 0
     assert t["peer_access"][0][0] == 1
+
+
+# ---- keras128 family: VALID first layer, feature dropout, dropout-aware unpool --------------------------------
+@pytest.mark.parametrize("B,C1,k", [(1, 32, 3), (128, 32, 3), (100, 32, 3), (5, 64, 3), (3, 192, 3), (4, 32, 5)])
+def test_conv1_valid_fwd_and_wgrad(B, C1, k):
+    torch.manual_seed(3)
+    Ho = 28 - k + 1
+    x = torch.rand(B, 784, device="cuda")
+    w = (torch.randn(k, k, 1, C1, device="cuda") * 0.2).to(bf16)
+    b = (torch.randn(C1, device="cuda") * 0.1).to(bf16)
+    out = torch.full((B, Ho, Ho, C1), float("nan"), device="cuda", dtype=bf16)
+    step = torch.zeros(1, device="cuda", dtype=torch.int32)
+    ring_l = torch.ones(8, device="cuda")
+    ring_c = torch.ones(8, device="cuda", dtype=torch.int32)
+    K.conv1_valid_fwd(x, w, b, out, step, bump_step=True, loss_ring=ring_l, correct_ring=ring_c)
+    assert step.item() == 1 and ring_l[1].item() == 0 and ring_c[1].item() == 0 and ring_l[2].item() == 1
+    wr = w.float().permute(3, 2, 0, 1).clone().requires_grad_(True)
+    br = b.float().clone().requires_grad_(True)
+    conv = F.relu(F.conv2d(x.view(B, 1, 28, 28), wr, br))
+    close(out, conv.permute(0, 2, 3, 1), 1e-2, 1e-2)
+    da1 = (torch.randn(B, Ho, Ho, C1, device="cuda") * 0.1).to(bf16)
+    # gradient through the ReLU mask of the kernel's own bf16 activations
+    pre = F.conv2d(x.view(B, 1, 28, 28), wr, br)
+    mask = (out.float() > 0).permute(0, 3, 1, 2)
+    (pre * mask * da1.float().permute(0, 3, 1, 2)).sum().backward()
+    dw = torch.zeros(k, k, 1, C1, device="cuda")
+    db = torch.zeros(C1, device="cuda")
+    K.conv1_valid_wgrad(x, da1, out, dw, db)
+    close(dw, wr.grad.permute(2, 3, 1, 0), 2e-2, 1e-3 * B)
+    close(db, br.grad, 2e-2, 1e-3 * B)
+
+
+@pytest.mark.parametrize("n,rate,layer", [(128 * 9216, 0.25, 0), (4 * 12 * 12 * 64, 0.25, 0), (1000, 0.5, 3), (64, 0.0, 1)])
+def test_dropout_bf16_matches_host_philox(n, rate, layer):
+    torch.manual_seed(4)
+    x = torch.randn(n, device="cuda").to(bf16)
+    step = torch.tensor([7], device="cuda", dtype=torch.int32)
+    out = torch.empty_like(x)
+    K.dropout_bf16(x, out, rate, 1234, step, layer)
+    keep = dropout_keep_mask(n, rate, 1234, 7, layer).cuda()
+    import numpy as np
+    sc = float(np.float32(1.0) / (np.float32(1.0) - np.float32(rate)))         # the kernel's fp32 keep-scale
+    ref = torch.where(keep, x.float() * sc, torch.zeros((), device="cuda")).to(bf16)
+    assert torch.equal(out, ref)
+    K.dropout_bf16(x, x, rate, 1234, step, layer)          # in place
+    assert torch.equal(x, ref)
+
+
+def test_unpool_relu_bwd_scaled():
+    torch.manual_seed(5)
+    B, HP, C = 6, 12, 64
+    pooled = torch.relu(torch.randn(B, HP, HP, C, device="cuda")).to(bf16)
+    pooled[torch.rand_like(pooled.float()) < 0.25] = 0          # dropped entries
+    am = torch.randint(0, 4, (B, HP, HP, C), device="cuda", dtype=torch.uint8)
+    dpool = torch.randn(B, HP, HP, C, device="cuda").to(bf16)
+    dy = torch.full((B, 2 * HP, 2 * HP, C), float("nan"), device="cuda", dtype=bf16)
+    db = torch.zeros(C, device="cuda")
+    sc = 1.0 / 0.75
+    K.unpool_relu_bwd(dpool, pooled, am, dy, db, gscale=sc)
+    g = torch.where(pooled.float() > 0, dpool.float() * sc, torch.zeros((), device="cuda")).to(bf16).float()
+    ref = torch.zeros(B, HP, 2, HP, 2, C, device="cuda")
+    for qd in range(4):
+        ref[:, :, qd >> 1, :, qd & 1, :] = torch.where(am == qd, g, torch.zeros((), device="cuda"))
+    assert torch.equal(dy.float(), ref.view(B, 2 * HP, 2 * HP, C))
+    close(db, torch.where(pooled.float() > 0, dpool.float() * sc, torch.zeros((), device="cuda")).sum((0, 1, 2)), 1e-2, 1e-2)
