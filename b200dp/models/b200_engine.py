@@ -274,7 +274,10 @@ class B200Engine(Engine):
         a2f = a2.view(B, self.F)
         wd = self.pv("dense.kernel", w)
         if self.tc_dense:
-            split = max(1, min(self.F // 64, (148 * 2) // max(1, (self.D // 64) * ((B + 127) // 128))))
+            # split-K: fill the machine, but every split adds one more fp32 red.add per output address — past ~32 adds the
+            # L2 atomics on the small [B,D] accumulator cost more than the extra CTAs buy (keras128: 12.0 us at 144 splits,
+            # 5.2 us at 24; profiles/kernel_bench_keras128.json)
+            split = max(1, min(self.F // 64, (148 * 2) // max(1, (self.D // 64) * ((B + 127) // 128)), 32))
             K.gemm_tc(a2f, wd, self.z[:B], B, self.D, self.F, b_mn_major=True, out_mode=2, split_k=split, block_n=64)
         else:
             K.gemm_simple(a2f, wd, self.z[:B], B, self.D, self.F)

@@ -32,6 +32,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "standin"])
     ap.add_argument("--batch", type=int, default=128, help="images per rank")
     ap.add_argument("--width", type=float, default=1.0)
+    ap.add_argument("--arch", default="mnist_cnn", choices=["mnist_cnn", "keras128"],
+                    help="mnist_cnn: the network as coded in the reference scripts (headline); keras128: the Keras-example shape")
     ap.add_argument("--algo", default="auto", choices=["auto", "oneshot", "twoshot", "nvls"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-tc", action="store_true")
@@ -139,7 +141,7 @@ def main():
     hvd.init(device="cuda")
     dev = hvd.device()
     B = args.batch
-    spec = hvd.get_spec("mnist_cnn", args.width)
+    spec = hvd.get_spec(args.arch, args.width)
     opt = hvd.DistributedOptimizer(hvd.Adam.keras(lr=0.001 * hvd.lr_scaler(args.adasum)),
                                    op=hvd.Adasum if args.adasum else hvd.Average, algo=args.algo)
     model = hvd.Model(spec, engine="b200", batch_size=B, use_graph=not args.no_graph, use_tc=not args.no_tc)
@@ -224,8 +226,10 @@ def main():
             "unit": "images/s", "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic 28x28 inputs, random-init weights", "impl": "ours",
-            "config": {"model": f"mnist_cnn(conv5x5x{eng.C1}-pool-conv5x5x{eng.C2}-pool-dense{eng.D}-dropout0.5-dense10, "
-                                f"{spec.num_params} params)", "global_batch": B * world_size, "per_gpu_batch": B, "seq_len": None,
+            "config": {"model": (f"mnist_cnn(conv5x5x{eng.C1}-pool-conv5x5x{eng.C2}-pool-dense{eng.D}-dropout0.5-dense10, "
+                                 if args.arch == "mnist_cnn" else
+                                 f"keras128(conv3x3x{eng.C1}-conv3x3x{eng.C2}-pool-dropout0.25-dense{eng.D}-dropout0.5-dense10, ")
+                                + f"{spec.num_params} params)", "global_batch": B * world_size, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world_size}", "optimizer": "Adam(lr=0.001*size) fused into the NVLink allreduce",
                        "allreduce": {"dense.kernel": ["oneshot", "twoshot", "nvls", "gemm+reduce-scatter fused, then two-shot tail"][eng.comm_dense[0][2]],
                                      "rest": ["oneshot", "twoshot", "nvls"][eng.comm_rest[1][2]], "wire": "fp32"},

@@ -29,6 +29,27 @@ class Net(nn.Module):
         return self.fc2(self.drop(F.relu(self.fc1(x))))
 
 
+class KerasNet(nn.Module):
+    """The Keras MNIST example shape (keras128 in b200dp.models.spec)."""
+
+    def __init__(self, width=1.0):
+        super().__init__()
+        c1, c2, d = int(round(32 * width)), int(round(64 * width)), int(round(128 * width))
+        self.conv1 = nn.Conv2d(1, c1, 3)
+        self.conv2 = nn.Conv2d(c1, c2, 3)
+        self.drop1 = nn.Dropout(0.25)
+        self.fc1 = nn.Linear(12 * 12 * c2, d)
+        self.drop2 = nn.Dropout(0.5)
+        self.fc2 = nn.Linear(d, 10)
+
+    def forward(self, x):
+        x = x.view(-1, 1, 28, 28)
+        x = F.relu(self.conv1(x))
+        x = self.drop1(F.max_pool2d(F.relu(self.conv2(x)), 2))
+        x = x.permute(0, 2, 3, 1).reshape(x.shape[0], -1)
+        return self.fc2(self.drop2(F.relu(self.fc1(x))))
+
+
 def run(args) -> int:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -39,7 +60,7 @@ def run(args) -> int:
         dist.init_process_group("nccl", device_id=dev)
     torch.backends.cudnn.benchmark = True
     B = args.batch
-    model = Net(args.width).to(dev).to(memory_format=torch.channels_last)
+    model = (KerasNet if getattr(args, "arch", "mnist_cnn") == "keras128" else Net)(args.width).to(dev).to(memory_format=torch.channels_last)
     net = nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=64, gradient_as_bucket_view=True) if world > 1 else model
     opt = torch.optim.Adam(model.parameters(), lr=0.001 * world, fused=True)
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
@@ -96,7 +117,7 @@ def run(args) -> int:
             "note": "stand-in for Horovod+NCCL (reference not installable offline): PyTorch DDP + NCCL + cuDNN/cuBLAS, bf16 autocast",
             "value": round(args.steps * B * world / (ms / 1e3), 1), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",
-            "dtype": "bf16", "data": "synthetic", "config": {"model": "mnist_cnn", "global_batch": B * world, "parallelism": f"dp{world}",
+            "dtype": "bf16", "data": "synthetic", "config": {"model": getattr(args, "arch", "mnist_cnn"), "global_batch": B * world, "parallelism": f"dp{world}",
                                                               "width": args.width},
             "e2e": {"value": round(args.steps * B * world / (ems / 1e3), 1), "unit": "images/s",
                     "h2d_bytes_per_step": B * 784 * 4 + B * 8, "d2h_bytes_per_step": 4}}))

@@ -246,6 +246,156 @@ __global__ void __launch_bounds__(256) conv1_valid_wgrad_kernel(const float* __r
   }
 }
 
+// 3x3 variants with eight channels per lane: 4 lanes cover a 32-channel chunk of one pixel, a warp works on 8 consecutive
+// pixels, so activations move as 16-byte accesses (512 contiguous bytes per warp) instead of 2-byte ones.  C1 % 8 == 0.
+__device__ __forceinline__ void unpack_bf16x8(const uint4 v, float* f) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    f[2 * j] = __uint_as_float(w[j] << 16);
+    f[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u);
+  }
+}
+
+__global__ void __launch_bounds__(256) conv1_valid3_fwd_v8_kernel(const float* __restrict__ x, const bf16* __restrict__ w,
+                                                                  const bf16* __restrict__ bias, bf16* __restrict__ out, int C1,
+                                                                  int* step_ptr, int bump_step, float* loss_ring,
+                                                                  int* correct_ring, int ring) {
+  constexpr int K = 3, HO = 26, NPIX = HO * HO;
+  __shared__ float img[28][29];
+  const int b = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
+  if (bump_step && b == 0 && blockIdx.y == 0 && threadIdx.x == 0 && step_ptr) {
+    const int s = *step_ptr + 1;
+    *step_ptr = s;
+    if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+  }
+  for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int sub = lane >> 2, cq = lane & 3;
+  const int per = (NPIX + gridDim.y - 1) / gridDim.y;
+  const int p0 = blockIdx.y * per, p1 = min(NPIX, p0 + per);
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + cq * 8;
+    if (c >= C1) continue;
+    float wr[K * K][8], bb[8];
+#pragma unroll
+    for (int t = 0; t < K * K; ++t) unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(w + t * C1 + c)), wr[t]);
+    unpack_bf16x8(__ldg(reinterpret_cast<const uint4*>(bias + c)), bb);
+    for (int p = p0 + warp * 8 + sub; p < p1; p += nwarp * 8) {
+      const int y = p / HO, xq = p % HO;
+      float acc[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = bb[e];
+#pragma unroll
+      for (int kh = 0; kh < K; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < K; ++kw) {
+          const float v = img[y + kh][xq + kw];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] = fmaf(v, wr[kh * K + kw][e], acc[e]);
+        }
+      const uint2 lo = pack_bf16x4(make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f)));
+      const uint2 hi = pack_bf16x4(make_float4(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f), fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f)));
+      *reinterpret_cast<uint4*>(out + ((size_t)b * NPIX + p) * C1 + c) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) conv1_valid3_wgrad_v8_kernel(const float* __restrict__ x, const bf16* __restrict__ da1,
+                                                                    const bf16* __restrict__ a1, float* __restrict__ dw,
+                                                                    float* __restrict__ dbias, int B, int C1) {
+  constexpr int K = 3, HO = 26, NPIX = HO * HO, NT = K * K + 1;
+  __shared__ float img[28][29];
+  __shared__ float red[8][NT][32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int sub = lane >> 2, cq = lane & 3;
+  const int per = (NPIX + gridDim.y - 1) / gridDim.y;
+  const int p0 = blockIdx.y * per, p1 = min(NPIX, p0 + per);
+  for (int c0 = 0; c0 < C1; c0 += 32) {
+    const int c = c0 + cq * 8;
+    const bool cvalid = c < C1;
+    float acc[NT][8];
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[t][e] = 0.f;
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
+      __syncthreads();
+      if (cvalid) {
+        for (int pb = p0 + warp * 8 + sub; pb < p1; pb += 2 * nwarp * 8) {
+          // two pixels per trip: four 16-byte loads in flight per lane
+          uint4 dv[2], av[2];
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int p = pb + i * nwarp * 8;
+            if (p < p1) {
+              const size_t o = ((size_t)b * NPIX + p) * C1 + c;
+              dv[i] = __ldg(reinterpret_cast<const uint4*>(da1 + o));
+              av[i] = __ldg(reinterpret_cast<const uint4*>(a1 + o));
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int p = pb + i * nwarp * 8;
+            if (p >= p1) continue;
+            float g[8], a[8];
+            unpack_bf16x8(dv[i], g);
+            unpack_bf16x8(av[i], a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) g[e] = a[e] > 0.f ? g[e] : 0.f;
+            const int y = p / HO, xq = p % HO;
+#pragma unroll
+            for (int kh = 0; kh < K; ++kh)
+#pragma unroll
+              for (int kw = 0; kw < K; ++kw) {
+                const float v = img[y + kh][xq + kw];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[kh * K + kw][e] = fmaf(v, g[e], acc[kh * K + kw][e]);
+              }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[K * K][e] += g[e];
+          }
+        }
+      }
+    }
+    // fold the 8 pixel slots of the warp (lane bits 2..4), then the warps, then one atomic per (tap, channel) per block
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float v = acc[t][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        acc[t][e] = v;
+      }
+    __syncthreads();
+    if (sub == 0) {
+#pragma unroll
+      for (int t = 0; t < NT; ++t)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) red[warp][t][cq * 8 + e] = acc[t][e];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NT * 32; i += blockDim.x) {
+      const int t = i >> 5, l = i & 31;
+      float sum = 0.f;
+      for (int wv = 0; wv < nwarp; ++wv) sum += red[wv][t][l];
+      if (c0 + l < C1) {
+        if (t < K * K) atomicAdd(dw + t * C1 + c0 + l, sum);
+        else atomicAdd(dbias + c0 + l, sum);
+      }
+    }
+  }
+}
+
 // Inverted dropout over a bf16 tensor (in place allowed): element i keeps its value * 1/(1-rate) when Philox lane i%4 of
 // counter (i/4, 0, step, layer) is >= rate * 2^32 — the same stream b200dp/utils/philox.py draws on the host.
 __global__ void __launch_bounds__(256) dropout_bf16_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, long long n4,
@@ -466,6 +616,65 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const bf16* __rest
   } else if (stride % C == 0) {
     const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (first < total) atomicAdd(dbias + (int)(first % C), bsum);
+  }
+}
+
+// Eight channels per thread (16-byte loads of dpool/pooled, 8-byte argmax, four 16-byte stores): the scalar kernel above
+// moves 2 bytes per memory instruction and is latency-bound.  Needs C % 8 == 0 and (for dbias) 256 % (C/8) == 0, which
+// keeps every thread on one channel group for the whole grid-stride loop.
+__global__ void __launch_bounds__(256) unpool_relu_bwd_v8_kernel(const bf16* __restrict__ dpool, const bf16* __restrict__ pooled,
+                                                                 const uint8_t* __restrict__ argmax, bf16* __restrict__ dy,
+                                                                 float* __restrict__ dbias, int HP, int WP, int C,
+                                                                 long long ngroups, float gscale) {
+  __shared__ float red[256][9];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int CG = C >> 3;
+  float bs[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) bs[e] = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const int W = 2 * WP;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < ngroups; i += stride) {
+    const int cg = (int)(i % CG);
+    long long p = i / CG;
+    const int pw = (int)(p % WP); p /= WP;
+    const int ph = (int)(p % HP);
+    const long long b = p / HP;
+    const uint4 dp = __ldg(reinterpret_cast<const uint4*>(dpool) + i);
+    const uint4 po = __ldg(reinterpret_cast<const uint4*>(pooled) + i);
+    const uint2 am = __ldg(reinterpret_cast<const uint2*>(argmax) + i);
+    const uint32_t dpw[4] = {dp.x, dp.y, dp.z, dp.w}, pow_[4] = {po.x, po.y, po.z, po.w};
+    uint32_t gb[8];           // gradient as bf16 bits, per channel
+    uint32_t qq[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const uint32_t dbits = (dpw[e >> 1] >> (16 * (e & 1))) & 0xFFFFu, pbits = (pow_[e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
+      const float pv = __uint_as_float(pbits << 16), dv = __uint_as_float(dbits << 16);
+      const float g = pv > 0.f ? dv * gscale : 0.f;
+      bs[e] += g;
+      gb[e] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(g));
+      qq[e] = ((e < 4 ? am.x : am.y) >> (8 * (e & 3))) & 0xFFu;
+    }
+    bf16* base = dy + ((((size_t)b * 2 * HP + 2 * ph) * W + 2 * pw) * C + cg * 8);
+#pragma unroll
+    for (int qd = 0; qd < 4; ++qd) {
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = (qq[2 * j] == (uint32_t)qd ? gb[2 * j] : 0u) | ((qq[2 * j + 1] == (uint32_t)qd ? gb[2 * j + 1] : 0u) << 16);
+      *reinterpret_cast<uint4*>(base + (size_t)(qd >> 1) * W * C + (qd & 1) * C) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+  if (dbias == nullptr) return;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[threadIdx.x][e] = bs[e];
+  __syncthreads();
+  if ((int)threadIdx.x < C) {
+    const int cg = threadIdx.x >> 3, e = threadIdx.x & 7;
+    float sum = 0.f;
+    for (int t = cg; t < 256; t += CG) sum += red[t][e];
+    atomicAdd(dbias + threadIdx.x, sum);
   }
 }
 
@@ -729,6 +938,13 @@ int b200_head_wgrad(const void* h, const void* dz, const float* dlogits, float* 
 int b200_unpool_relu_bwd_scaled(const void* dpool, const void* pooled, const uint8_t* argmax, void* dy, float* dbias, int B,
                                 int HP, int WP, int C, float gscale, void* stream) {
   const long long total = (long long)B * HP * WP * C;
+  const bool aligned = (((uintptr_t)dpool | (uintptr_t)pooled | (uintptr_t)dy) & 15) == 0 && ((uintptr_t)argmax & 7) == 0;
+  if (C % 8 == 0 && C <= 256 && 256 % (C / 8) == 0 && aligned) {
+    const long long ngroups = total / 8;
+    B200_CHECK(launch_pdl(unpool_relu_bwd_v8_kernel, dim3(grid_for(ngroups, 256, 148 * 8)), dim3(256), 0, (cudaStream_t)stream,
+                          (const bf16*)dpool, (const bf16*)pooled, argmax, (bf16*)dy, dbias, HP, WP, C, ngroups, gscale));
+    return B200_OK;
+  }
   int grid = grid_for(total, 256, 148 * 4);
   if (dbias && 256 % C != 0) {
     // keep the stride a multiple of C so a thread never changes channel
@@ -749,7 +965,8 @@ int b200_conv1_valid_fwd(const float* x, const void* w, const void* bias, void* 
                          int bump_step, float* loss_ring, int* correct_ring, int ring, void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1_valid: bad shape B=%d C1=%d", B, C1);
   B200_REQUIRE(k == 3 || k == 5, "conv1_valid: kernel size %d not instantiated (3 or 5)", k);
-  auto kern = k == 3 ? conv1_valid_fwd_kernel<3> : conv1_valid_fwd_kernel<5>;
+  const bool v8 = k == 3 && C1 % 8 == 0 && (((uintptr_t)w | (uintptr_t)bias | (uintptr_t)out) & 15) == 0;
+  auto kern = v8 ? conv1_valid3_fwd_v8_kernel : (k == 3 ? conv1_valid_fwd_kernel<3> : conv1_valid_fwd_kernel<5>);
   B200_CHECK(launch_pdl(kern, dim3(B, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)w, (const bf16*)bias, (bf16*)out, C1,
                         step_ptr, bump_step, loss_ring, correct_ring, ring));
   return B200_OK;
@@ -759,7 +976,8 @@ int b200_conv1_valid_wgrad(const float* x, const void* da1, const void* a1, floa
                            void* stream) {
   B200_REQUIRE(B > 0 && C1 > 0, "conv1_valid wgrad: bad shape");
   B200_REQUIRE(k == 3 || k == 5, "conv1_valid wgrad: kernel size %d not instantiated (3 or 5)", k);
-  auto kern = k == 3 ? conv1_valid_wgrad_kernel<3> : conv1_valid_wgrad_kernel<5>;
+  const bool v8 = k == 3 && C1 % 8 == 0 && (((uintptr_t)da1 | (uintptr_t)a1) & 15) == 0;
+  auto kern = v8 ? conv1_valid3_wgrad_v8_kernel : (k == 3 ? conv1_valid_wgrad_kernel<3> : conv1_valid_wgrad_kernel<5>);
   const int grid = B < 74 ? B : 74;
   B200_CHECK(launch_pdl(kern, dim3(grid, 4), dim3(256), 0, (cudaStream_t)stream, x, (const bf16*)da1, (const bf16*)a1, dw, dbias, B, C1));
   return B200_OK;

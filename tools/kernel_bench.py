@@ -12,10 +12,12 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=128)
 ap.add_argument("--width", type=float, default=1.0)
 ap.add_argument("--reps", type=int, default=20)
+ap.add_argument("--arch", default="mnist_cnn", choices=["mnist_cnn", "keras128"])
+ap.add_argument("--dense-splits", default="", help="comma list: also time the dense forward GEMM at these split-K factors")
 ap.add_argument("--out", default="gpurun_out/kernel_bench.json")
 a = ap.parse_args()
 hvd.init(device="cuda")
-e = hvd.make_engine(hvd.get_spec("mnist_cnn", a.width), hvd.DistributedOptimizer(hvd.Adam(1e-3)), engine="b200", batch_size=a.batch, use_graph=False)
+e = hvd.make_engine(hvd.get_spec(a.arch, a.width), hvd.DistributedOptimizer(hvd.Adam(1e-3)), engine="b200", batch_size=a.batch, use_graph=False)
 B = a.batch
 e.x.copy_(torch.rand(B, 784, device="cuda")); e.y.copy_(torch.randint(0, 10, (B,), device="cuda", dtype=torch.int32))
 for _ in range(3):
@@ -23,11 +25,18 @@ for _ in range(3):
 torch.cuda.synchronize()
 w, g = e.w16, e.grads[0]
 a2f = e.a2[:B].view(B, e.F); dpool = e.dpool[:B].view(B, e.F)
-split = max(1, min(e.F // 64, (148 * 2) // max(1, (e.D // 64) * ((B + 127) // 128))))
+split = max(1, min(e.F // 64, (148 * 2) // max(1, (e.D // 64) * ((B + 127) // 128)), 32))
 T4 = e.T * 4
+if e.keras:
+    conv1 = {"conv1_valid_fwd": lambda: K.conv1_valid_fwd(e.x[:B], e.pv("conv1.kernel", w), e.pv("conv1.bias", w), e.a1[:B]),
+             "feature_dropout": lambda: K.dropout_bf16(e.a2[:B], e.a2[:B], e.feat_drop, 1, e.step_dev, 0)}
+    conv1w = {"conv1_valid_wgrad": lambda: K.conv1_valid_wgrad(e.x[:B], e.da1[:B], e.a1[:B], e.pv("conv1.kernel", g), e.pv("conv1.bias", g))}
+else:
+    conv1 = {"conv1_pool_fwd": lambda: K.conv1_pool_fwd(e.x[:B], e.pv("conv1.kernel", w), e.pv("conv1.bias", w), e.a1[:B], e.am1[:B])}
+    conv1w = {"conv1_wgrad": lambda: K.conv1_wgrad(e.x[:B], e.da1[:B], e.a1[:B], e.am1[:B], e.pv("conv1.kernel", g), e.pv("conv1.bias", g))}
 ops = {
-    "conv1_pool_fwd": lambda: K.conv1_pool_fwd(e.x[:B], e.pv("conv1.kernel", w), e.pv("conv1.bias", w), e.a1[:B], e.am1[:B]),
-    "conv2_fwd(tc)": lambda: K.conv_tc_fwd(e.a1[:B], e.pv("conv2.kernel", w), e.pv("conv2.bias", w), e.a2[:B], e.am2[:B], relu=True, pool=True),
+    **conv1,
+    "conv2_fwd(tc)": lambda: K.conv_tc_fwd(e.a1[:B], e.pv("conv2.kernel", w), e.pv("conv2.bias", w), e.a2[:B], e.am2[:B], relu=True, pool=True, pad=e.PAD2),
     "dense_fwd(tc,splitK)": lambda: K.gemm_tc(a2f, e.pv("dense.kernel", w), e.z[:B], B, e.D, e.F, b_mn_major=True, out_mode=2, split_k=split, block_n=64),
     "head_fwd_bwd": lambda: K.head_fwd_bwd(e.z[:B], e.pv("dense.bias", w), e.pv("out.kernel", w), e.pv("out.bias", w), e.y[:B], e.h[:B], e.dz[:B],
                                            e.dlogits[:B], None, e.loss_ring, e.correct_ring, drop_rate=0.5, training=True, seed=1, step_ptr=e.step_dev, ring=1024),
@@ -35,12 +44,16 @@ ops = {
     "dense_wgrad(tc)": lambda: K.gemm_tc(a2f, e.dz[:B], e.pv("dense.kernel", g), e.F, e.D, B, a_mn_major=True, b_mn_major=True, out_mode=0, block_n=128),
     "dense_dgrad(tc)": lambda: K.gemm_tc(e.dz[:B], e.pv("dense.kernel", w), dpool, B, e.F, e.D, out_mode=1, block_n=32),
     "unpool_relu_bwd": lambda: K.unpool_relu_bwd(e.dpool[:B], e.a2[:B], e.am2[:B], e.dy2[:B], e.pv("conv2.bias", g)),
-    "conv2_wgrad(tc)": lambda: K.conv_tc_wgrad(e.a1[:B], e.dy2[:B], e.pv("conv2.kernel", g), None),
-    "conv2_dgrad(tc)": lambda: K.conv_tc_dgrad(e.dy2[:B], e.pv("conv2.kernel", w), e.da1[:B]),
-    "conv1_wgrad": lambda: K.conv1_wgrad(e.x[:B], e.da1[:B], e.a1[:B], e.am1[:B], e.pv("conv1.kernel", g), e.pv("conv1.bias", g)),
+    "conv2_wgrad(tc)": lambda: K.conv_tc_wgrad(e.a1[:B], e.dy2[:B], e.pv("conv2.kernel", g), None, pad=e.PAD2),
+    "conv2_dgrad(tc)": lambda: K.conv_tc_dgrad(e.dy2[:B], e.pv("conv2.kernel", w), e.da1[:B], pad=e.PAD2),
+    **conv1w,
     "fused_adam(dense bucket)": lambda: e._comm(0, e.comm_dense, 0),
     "fused_adam(rest)": lambda: e._comm(1, e.comm_rest, 0),
 }
+for sp in [int(v) for v in a.dense_splits.split(",") if v]:
+    ops[f"dense_fwd split={sp}"] = (lambda sp=sp: K.gemm_tc(a2f, e.pv("dense.kernel", w), e.z[:B], B, e.D, e.F, b_mn_major=True, out_mode=2, split_k=sp, block_n=64))
+    if e.D % 128 == 0:
+        ops[f"dense_fwd split={sp} bn128"] = (lambda sp=sp: K.gemm_tc(a2f, e.pv("dense.kernel", w), e.z[:B], B, e.D, e.F, b_mn_major=True, out_mode=2, split_k=sp, block_n=128))
 res = {}
 print(f"{'kernel':28s} {'us/launch':>10s}")
 for name, fn in ops.items():
@@ -58,6 +71,6 @@ for name, fn in ops.items():
     us = e0.elapsed_time(e1) * 1e3 / (5 * a.reps)
     res[name] = us
     print(f"{name:28s} {us:10.2f}")
-print(f"{'sum':28s} {sum(res.values()):10.2f}")
+print(f"{'sum':28s} {sum(v for k, v in res.items() if 'split=' not in k):10.2f}")
 os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
-json.dump({"batch": B, "width": a.width, "us_per_launch": res}, open(a.out, "w"), indent=1)
+json.dump({"arch": a.arch, "batch": B, "width": a.width, "us_per_launch": res}, open(a.out, "w"), indent=1)
