@@ -60,22 +60,8 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, const float* 
       if (p.relu) v[j] = fmaxf(v[j], 0.f);
     }
     if (p.pool) {
-      uint32_t packed[8];
-      uint32_t am[4] = {0, 0, 0, 0};
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float v01 = __shfl_xor_sync(0xffffffffu, v[j], 1);
-        const float v10 = __shfl_xor_sync(0xffffffffu, v[j], 16);
-        const float v11 = __shfl_xor_sync(0xffffffffu, v[j], 17);
-        float best = v[j];
-        uint32_t bi = 0;
-        if (v01 > best) { best = v01; bi = 1; }
-        if (v10 > best) { best = v10; bi = 2; }
-        if (v11 > best) { best = v11; bi = 3; }
-        const uint32_t hb = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(best));
-        if (j & 1) packed[j >> 1] |= hb << 16; else packed[j >> 1] = hb;
-        am[j >> 2] |= bi << (8 * (j & 3));
-      }
+      uint32_t packed[8], am[4];
+      pool2x2_bf16x16<1, 16>(v, packed, am);
       if (lane < 16 && !(lane & 1) && ww < p.W && h < p.H) {
         const size_t o = (((size_t)img * (p.H / 2) + h / 2) * (p.W / 2) + ww / 2) * p.N + c;
         *reinterpret_cast<uint4*>(p.out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);

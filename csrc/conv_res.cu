@@ -1,0 +1,307 @@
+// Persistent implicit-GEMM convolution with a shared-memory-resident image of ANY size that fits (fwd and dgrad),
+// any padding 0..k-1 — the generalisation of conv_halo.cu (which is specialised to <=16x16 SAME images).
+//
+// conv_tc.cu re-loads a shifted TMA box per filter tap, so every activation byte crosses L2->SM k*k times: the keras128
+// second layer (3x3 VALID on 26x26x32, 128 images) moves 83 MB for its forward and 184 MB for its dgrad and is bound by
+// exactly that (17 us / 31 us measured).  Here each image is loaded ONCE into the UMMA no-swizzle canonical layout
+//   [channel chunk of 8][stored row][P stored pixels][8 channels]        (16 B per pixel per chunk)
+// with a zero margin of m rows/columns on the top/left (m = pad forward, k-1-pad for dgrad) and zeros after the real
+// pixels, and an M tile is a 16-row x 8-column patch of OUTPUT pixels: 8 consecutive pixels of a row are one 128-byte
+// core matrix, the 16 rows of the patch are a uniform stride apart (SBO = P*16 B), the 8-channel chunks are LBO apart.
+// A filter tap is then just a different 16-byte-aligned start address: (kh', kw') stored pixels further on.  With the
+// 16x8 patch the 2x2 max-pool partners of a pixel are TMEM lanes ^1 (column) and ^8 (row) of the same warp.
+//
+// The image arrives in two halves (rows feeding the first 16 output rows, then the rest) on separate mbarriers, so the
+// first row of tiles starts while the second half is still in flight; accumulators rotate through a 4-deep TMEM ring so
+// the epilogue of one tile overlaps the MMAs of the next.
+//
+// Replaces cuDNN conv2d fwd/dgrad behind Keras Conv2D (horovod/tensorflow_mnist_gpu.py:47-56) — SURVEY K5/K6/K13.
+#include <stdlib.h>
+
+#include "../include/b200dp.h"
+#include "tc_sm100.cuh"
+
+namespace {
+
+using namespace tc;
+
+constexpr int NACC = 4;              // TMEM accumulator ring depth
+
+struct ResParams {
+  int B, Hs, Ws, Ho, Wo, Ci, Co, k;
+  int mode;            // 0 forward, 1 dgrad
+  int Cred, N;         // reduction channels, produced channels
+  int m;               // zero margin (stored rows/cols before the first real pixel)
+  int P, R;            // stored pixels per row, stored rows
+  int TH, TW;          // output tiles per image: ceil(Ho/16) x ceil(Wo/8)
+  int hsplit;          // source rows [0,hsplit) form the first half of the image
+  int chunk_bytes;     // R * P * 16
+  int img_bytes;       // (Cred/8) * chunk_bytes
+  int nbuf;            // image buffers (2 when they fit, else 1)
+  int wtile_bytes;     // one tap's weight tile
+  int relu, pool;
+  const bf16* act;
+  const bf16* bias;
+  bf16* out;
+  uint8_t* argmax;
+  uint32_t tmem_cols;
+  uint32_t ck_shift, ws_magic;   // pieces -> (pixel, chunk) by shift; pixel -> row by multiply-high (no integer divides in the loader)
+  int dbg;             // experiment switches (B200DP_RES_DBG): 1 one MMA per tile, 2 skip image loads, 8 skip epilogue math
+};
+
+// TMEM lane r of the tile = output pixel (h0 + r/8, w0 + r%8); warp q owns lanes 32q..32q+31 = rows 4q..4q+3.
+__device__ __forceinline__ void res_epilogue(const ResParams& p, const float* sbias, uint32_t taddr, int img, int h0, int w0,
+                                             int lane, int q) {
+  const int h = h0 + 4 * q + (lane >> 3), w = w0 + (lane & 7);
+  for (int c = 0; c < p.N; c += 16) {
+    uint32_t r[16];
+    tmem_ld_32x16(taddr + c, r);
+    tmem_ld_wait();
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      v[j] = __uint_as_float(r[j]) + sbias[c + j];
+      if (p.relu) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (p.pool) {
+      uint32_t packed[8], am[4];
+      pool2x2_bf16x16<1, 8>(v, packed, am);
+      if (!(lane & 9) && w < p.Wo && h < p.Ho) {
+        const size_t o = (((size_t)img * (p.Ho / 2) + h / 2) * (p.Wo / 2) + w / 2) * p.N + c;
+        *reinterpret_cast<uint4*>(p.out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        *reinterpret_cast<uint4*>(p.out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+        if (p.argmax) *reinterpret_cast<uint4*>(p.argmax + o) = make_uint4(am[0], am[1], am[2], am[3]);
+      }
+    } else if (w < p.Wo && h < p.Ho) {
+      const size_t o = (((size_t)img * p.Ho + h) * p.Wo + w) * p.N + c;
+      uint2 lo = pack_bf16x4(make_float4(v[0], v[1], v[2], v[3])), l2 = pack_bf16x4(make_float4(v[4], v[5], v[6], v[7]));
+      uint2 hi = pack_bf16x4(make_float4(v[8], v[9], v[10], v[11])), h2 = pack_bf16x4(make_float4(v[12], v[13], v[14], v[15]));
+      *reinterpret_cast<uint4*>(p.out + o) = make_uint4(lo.x, lo.y, l2.x, l2.y);
+      *reinterpret_cast<uint4*>(p.out + o + 8) = make_uint4(hi.x, hi.y, h2.x, h2.y);
+    }
+  }
+}
+
+template <int KK, int KSTEPS, int MODE>
+__global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant__ CUtensorMap tmW, const ResParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int ntaps = KK * KK;
+  uint8_t* sW = smem;                                             // ntaps tiles, 1024-aligned each
+  uint8_t* sImg0 = sW + ntaps * p.wtile_bytes;
+  uint64_t* wfull = (uint64_t*)(sImg0 + p.nbuf * p.img_bytes);
+  uint64_t* afull = wfull + ntaps;                                // [buf][half]
+  uint64_t* aempty = afull + 4;                                   // [buf]
+  uint64_t* tfull = aempty + 2;                                   // [acc]
+  uint64_t* tempty = tfull + NACC;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + NACC);
+  float* sbias = (float*)(tmem_slot + 4);                         // p.N floats (zeros when the conv has no bias)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nimg = (p.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;    // images this CTA handles
+  const int T = p.TH * p.TW;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmW);
+    for (int t = 0; t < ntaps; ++t) mbar_init(wfull + t, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(afull + i, 128);
+    for (int i = 0; i < 2; ++i) mbar_init(aempty + i, 1);
+    for (int i = 0; i < NACC; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
+    fence_barrier_init();
+  }
+  // Zero the image buffers once: the loader warps only ever write real pixels, so the margins stay zero for every image.
+  // Without a margin (VALID forward) nothing needs zeroing: stale bytes only feed accumulator rows of pixels outside the
+  // output, and an MMA row depends on its own A row alone.
+  if (p.m > 0) {
+    uint4* z = reinterpret_cast<uint4*>(sImg0);
+    const int n16 = p.nbuf * p.img_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  fence_proxy_async();
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
+  pdl_launch_dependents();
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+  __syncthreads();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int t = 0; t < ntaps; ++t) {
+        mbar_arrive_expect_tx(wfull + t, (uint32_t)p.wtile_bytes);
+        tma_load_2d(sW + t * p.wtile_bytes, &tmW, wfull + t, 0, t * p.Ci);     // [Ci rows][Co cols]
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // Uniform loops; one elected lane issues.  An A descriptor is a constant high word plus
+    // (image base + tile origin + tap offset + chunk offset) in the 14-bit start-address field.
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(128, p.N, 0, MODE == 0 ? 1 : 0);
+    const uint64_t a_hi = make_smem_desc(0, (uint32_t)p.chunk_bytes, (uint32_t)p.P * 16u, SW_NONE);
+    const uint64_t b_hi = MODE == 0 ? make_smem_desc(0, 0, 1024, SW_128B) : make_smem_desc(0, 16, 1024, SW_128B);
+    constexpr uint32_t b_step = (MODE == 0 ? 2048u : 32u) >> 4;
+    const uint32_t a_step = (uint32_t)(2 * p.chunk_bytes) >> 4;
+    const uint32_t w_lo = (smem_u32(sW) & 0x3FFFFu) >> 4, w_step = (uint32_t)p.wtile_bytes >> 4;
+    int j = 0;                                                     // running tile counter -> accumulator ring slot
+    for (int it = 0; it < nimg; ++it) {
+      const int buf = p.nbuf == 2 ? (it & 1) : 0;
+      const uint32_t aph = (uint32_t)(p.nbuf == 2 ? (it >> 1) : it) & 1u;
+      const uint32_t i_lo = (smem_u32(sImg0 + buf * p.img_bytes) & 0x3FFFFu) >> 4;
+      for (int th = 0; th < p.TH; ++th) {
+        if (th < 2) { mbar_wait(afull + buf * 2 + th, aph, 32); tc_fence_after(); }
+        for (int tw = 0; tw < p.TW; ++tw, ++j) {
+          const int acc = j % NACC;
+          mbar_wait(tempty + acc, (((uint32_t)(j / NACC)) & 1u) ^ 1u, 33);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.N);
+          const uint32_t org = i_lo + (uint32_t)(th * 16 * p.P + tw * 8);
+#pragma unroll
+          for (int t = 0; t < ntaps; ++t) {
+            if (j == 0) { mbar_wait(wfull + t, 0, 34); tc_fence_after(); }
+            const int kh = t / KK, kw = t % KK;
+            // stored-pixel offset of the tap: forward (kh, kw); dgrad (k-1-kh, k-1-kw)
+            const int oh = MODE == 0 ? kh : KK - 1 - kh, ow = MODE == 0 ? kw : KK - 1 - kw;
+            const uint32_t a_lo = org + (uint32_t)(oh * p.P + ow);
+            if (leader && !((p.dbg & 1) && t > 0)) {
+#pragma unroll
+              for (int ks = 0; ks < KSTEPS; ++ks)
+                umma_bf16(d_tmem, a_hi + (uint64_t)(a_lo + ks * a_step), b_hi + (uint64_t)(w_lo + t * w_step + ks * b_step), idesc,
+                          (t > 0 || ks > 0) ? 1u : 0u);
+            }
+          }
+          if (leader) umma_commit(tfull + acc);
+          __syncwarp();
+        }
+      }
+      if (leader) umma_commit(aempty + buf);          // every tile's MMAs have consumed the image buffer
+      __syncwarp();
+    }
+  } else if (warp >= 6) {
+    // ===== image loaders (4 warps): coalesced 16-byte global loads scattered into [chunk][row][P px][8 ch]
+    const int lt = threadIdx.x - 192;
+    const int CK = p.Cred / 8;
+    const int pieces = p.Hs * p.Ws * CK;
+    const int split = min(p.hsplit, p.Hs) * p.Ws * CK;
+    for (int it = 0; it < nimg; ++it) {
+      const int buf = p.nbuf == 2 ? (it & 1) : 0;
+      const uint32_t eph = ((uint32_t)(p.nbuf == 2 ? (it >> 1) : it) & 1u) ^ 1u;
+      mbar_wait(aempty + buf, eph, 31);
+      const int img = blockIdx.x + it * gridDim.x;
+      const uint4* src = reinterpret_cast<const uint4*>(p.act + (size_t)img * p.Hs * p.Ws * p.Cred);
+      uint8_t* dst = sImg0 + buf * p.img_bytes;
+      // LDGSTS: every 16-byte piece of the image is in flight at once, nothing is staged through registers; the two halves
+      // are separate commit groups so the first row of tiles is released as soon as ITS rows have landed
+      for (int half = 0; half < 2; ++half) {
+        const int lo = half ? split : 0, hi = half ? pieces : split;
+        for (int idx = lo + lt; idx < hi; idx += 128) {
+          const int pixel = idx >> p.ck_shift, chunk = idx & (CK - 1);
+          const int h = (int)__umulhi((uint32_t)pixel, p.ws_magic), w = pixel - h * p.Ws;
+          if (p.dbg & 2) continue;
+          cp_async16(dst + chunk * p.chunk_bytes + ((h + p.m) * p.P + (w + p.m)) * 16, src + idx);
+        }
+        cp_async_commit();
+      }
+      cp_async_wait_group<1>();
+      fence_proxy_async();                   // generic-proxy writes -> visible to the tensor core's async proxy
+      mbar_arrive(afull + buf * 2 + 0);
+      cp_async_wait_group<0>();
+      fence_proxy_async();
+      mbar_arrive(afull + buf * 2 + 1);
+    }
+  } else {
+    const int q = warp & 3;
+    int j = 0;
+    for (int it = 0; it < nimg; ++it) {
+      const int img = blockIdx.x + it * gridDim.x;
+      for (int tile = 0; tile < T; ++tile, ++j) {
+        const int acc = j % NACC;
+        mbar_wait(tfull + acc, ((uint32_t)(j / NACC)) & 1u, 35);
+        tc_fence_after();
+        if (!(p.dbg & 8)) res_epilogue(p, sbias, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.N), img, (tile / p.TW) * 16,
+                     (tile % p.TW) * 8, lane, q);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty + acc);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+}  // namespace
+
+// Returns B200_ERR_UNSUPPORTED (without setting an error) when the shape does not fit this kernel.
+// H x W: forward-input size (as everywhere in conv_tc.cu); pad: forward padding.
+int b200_conv_res_launch(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H,
+                         int W, int Ci, int Co, int k, int pad, int relu, int pool, cudaStream_t st) {
+  const int Cred = mode == 0 ? Ci : Co, N = mode == 0 ? Co : Ci;
+  const int ntaps = k * k;
+  if ((k != 3 && k != 5) || pad < 0 || pad >= k) return B200_ERR_UNSUPPORTED;
+  const int Hf = H + 2 * pad - k + 1, Wf = W + 2 * pad - k + 1;
+  if (Hf < 1 || Wf < 1) return B200_ERR_UNSUPPORTED;
+  if (mode == 0 && (N != 64 || Cred != 32)) return B200_ERR_UNSUPPORTED;                 // MN-major B tile: one 128-byte row of co
+  if (mode == 1 && (Cred != 64 || N % 16 != 0 || N > 128)) return B200_ERR_UNSUPPORTED;  // K-major B tile: 128-byte rows of co
+  ResParams p;
+  p.B = B; p.Ci = Ci; p.Co = Co; p.k = k; p.mode = mode; p.Cred = Cred; p.N = N;
+  p.Hs = mode == 0 ? H : Hf; p.Ws = mode == 0 ? W : Wf;
+  p.Ho = mode == 0 ? Hf : H; p.Wo = mode == 0 ? Wf : W;
+  if (pool && (p.Ho % 2 || p.Wo % 2)) return B200_ERR_UNSUPPORTED;
+  p.m = mode == 0 ? pad : k - 1 - pad;
+  p.P = p.Ws + 2 * p.m;
+  p.TH = (p.Ho + 15) / 16;
+  p.TW = (p.Wo + 7) / 8;
+  p.R = p.TH * 16 + k - 1 + (p.TW * 8 + k - 1 + p.P - 1) / p.P;
+  if (p.R < p.Hs + 2 * p.m) p.R = p.Hs + 2 * p.m;
+  p.hsplit = 16 + k - 1 - p.m;
+  p.chunk_bytes = p.R * p.P * 16;
+  p.img_bytes = (Cred / 8) * p.chunk_bytes;
+  p.wtile_bytes = Ci * Co * 2;
+  if (p.wtile_bytes % 1024 != 0 || p.chunk_bytes >= (1 << 18) || p.P * 16 >= (1 << 18)) return B200_ERR_UNSUPPORTED;
+  p.relu = relu; p.pool = pool; p.act = (const bf16*)act; p.bias = (const bf16*)bias; p.out = (bf16*)out; p.argmax = argmax;
+  uint32_t cols = 32;
+  while ((int)cols < NACC * N) cols <<= 1;
+  if (cols > 512) return B200_ERR_UNSUPPORTED;
+  p.tmem_cols = cols;
+  { const char* e = getenv("B200DP_RES_DBG"); p.dbg = e ? atoi(e) : 0; }
+  if ((Cred / 8) & (Cred / 8 - 1)) return B200_ERR_UNSUPPORTED;
+  p.ck_shift = 0;
+  while ((1 << p.ck_shift) < Cred / 8) ++p.ck_shift;
+  if (p.Ws < 2 || (long)p.Hs * p.Ws * p.Ws >= (1l << 31)) return B200_ERR_UNSUPPORTED;
+  p.ws_magic = (uint32_t)(((1ull << 32) + p.Ws - 1) / p.Ws);      // umulhi(pixel, magic) == pixel / Ws exactly while pixel * Ws < 2^32
+  const size_t fixed = 1024 + (size_t)ntaps * p.wtile_bytes + (ntaps + 6 + 2 * NACC) * 8 + 64 + (size_t)N * 4;
+  const int grid = B < 148 ? B : 148;
+  p.nbuf = (B > grid && fixed + 2 * (size_t)p.img_bytes <= 220 * 1024) ? 2 : 1;   // a second buffer only pays with >1 image per CTA
+  const size_t smem = fixed + (size_t)p.nbuf * p.img_bytes;
+  if (smem > 220 * 1024) return B200_ERR_UNSUPPORTED;
+
+  CUtensorMap tmW;
+  int rc;
+  {
+    const uint64_t dims[2] = {(uint64_t)Co, (uint64_t)ntaps * Ci}, str[1] = {(uint64_t)Co * 2};
+    const uint32_t box[2] = {(uint32_t)Co, (uint32_t)Ci};
+    if ((rc = tc::make_tmap_bf16(&tmW, w, 2, dims, str, box, 128))) return rc;
+  }
+  const int ksteps = Cred / 16;
+  void (*kern)(const CUtensorMap, const ResParams) = nullptr;
+  if (k == 5 && mode == 0 && ksteps == 2) kern = conv_res_kernel<5, 2, 0>;
+  else if (k == 5 && mode == 1 && ksteps == 4) kern = conv_res_kernel<5, 4, 1>;
+  else if (k == 3 && mode == 0 && ksteps == 2) kern = conv_res_kernel<3, 2, 0>;
+  else if (k == 3 && mode == 1 && ksteps == 4) kern = conv_res_kernel<3, 4, 1>;
+  else return B200_ERR_UNSUPPORTED;
+  static const void* configured[8] = {};
+  bool seen = false;
+  for (const void* c : configured) seen |= (c == (const void*)kern);
+  if (!seen) {
+    B200_CHECK(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    for (const void*& c : configured)
+      if (c == nullptr) { c = (const void*)kern; break; }
+  }
+  B200_CHECK(launch_pdl(kern, dim3(grid), dim3(320), smem, st, tmW, p));
+  return B200_OK;
+}

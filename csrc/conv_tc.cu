@@ -146,22 +146,8 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         if (p.relu) v[j] = fmaxf(v[j], 0.f);
       }
       if (p.pool) {
-        uint32_t packed[8];
-        uint32_t am[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float v01 = __shfl_xor_sync(0xffffffffu, v[j], 1);
-          const float v10 = __shfl_xor_sync(0xffffffffu, v[j], 16);
-          const float v11 = __shfl_xor_sync(0xffffffffu, v[j], 17);
-          float best = v[j];
-          uint32_t bi = 0;
-          if (v01 > best) { best = v01; bi = 1; }
-          if (v10 > best) { best = v10; bi = 2; }
-          if (v11 > best) { best = v11; bi = 3; }
-          const uint32_t hb = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(best));
-          if (j & 1) packed[j >> 1] |= hb << 16; else packed[j >> 1] = hb;
-          am[j >> 2] |= bi << (8 * (j & 3));
-        }
+        uint32_t packed[8], am[4];
+        pool2x2_bf16x16<1, 16>(v, packed, am);
         if (lane < 16 && !(lane & 1) && ww < p.Wo && h < p.Ho) {
           const size_t o = (((size_t)img * (p.Ho / 2) + h / 2) * (p.Wo / 2) + ww / 2) * Cout + n0 + c;
           *reinterpret_cast<uint4*>(p.out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
@@ -393,6 +379,15 @@ int launch_conv(int mode, const void* act, const void* w, const void* bias, void
 int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H,
                           int W, int Ci, int Co, int k, int relu, int pool, cudaStream_t st);
 
+int b200_conv_res_launch(int mode, const void* act, const void* w, const void* bias, void* out, uint8_t* argmax, int B, int H,
+                         int W, int Ci, int Co, int k, int pad, int relu, int pool, cudaStream_t st);
+
+// B200DP_CONV_RES=0 keeps larger / VALID images on the shifted-TMA-box kernel instead of the smem-resident one
+static bool res_enabled() {
+  const char* e = getenv("B200DP_CONV_RES");
+  return !(e && e[0] == '0');
+}
+
 static bool halo_enabled() {
   const char* e = getenv("B200DP_CONV_HALO");
   return !(e && e[0] == '0');
@@ -404,6 +399,10 @@ int b200_conv_tc_fwd_pad(const void* in, const void* w, const void* bias, void* 
                          int Ci, int Co, int k, int pad, int relu, int pool, void* stream) {
   if (halo_enabled() && pad == k / 2 && (k & 1)) {
     const int rc = b200_conv_halo_launch(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, relu, pool, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (res_enabled()) {
+    const int rc = b200_conv_res_launch(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, pad, relu, pool, (cudaStream_t)stream);
     if (rc != B200_ERR_UNSUPPORTED) return rc;
   }
   return launch_conv(0, in, w, bias, out, argmax, B, H, W, Ci, Co, k, pad, relu, pool, (cudaStream_t)stream);
@@ -419,6 +418,10 @@ int b200_conv_tc_dgrad_pad(const void* dout, const void* w, void* din, int B, in
                            void* stream) {
   if (halo_enabled() && pad == k / 2 && (k & 1)) {
     const int rc = b200_conv_halo_launch(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, 0, 0, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (res_enabled()) {
+    const int rc = b200_conv_res_launch(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, pad, 0, 0, (cudaStream_t)stream);
     if (rc != B200_ERR_UNSUPPORTED) return rc;
   }
   return launch_conv(1, dout, w, nullptr, din, nullptr, B, H, W, Ci, Co, k, pad, 0, 0, (cudaStream_t)stream);

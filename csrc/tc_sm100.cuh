@@ -4,6 +4,7 @@
 // the GPU) because a deadlocked kernel on a shared box costs a strike.
 #pragma once
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -120,6 +121,43 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16])
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---------------------------------------------------------------- pooling epilogue helper
+// 2x2 max-pool of 16 consecutive channels held one pixel per lane: the window partners of this lane's pixel are lanes
+// ^XW (next column), ^XH (next row) and ^(XW|XH).  Values are rounded to bf16 FIRST (max commutes with the monotonic
+// rounding, so the result equals round(max)) and travel as bf16x2, which halves the shuffles and turns the compare chain
+// into HMNMX2/HSET2 on two channels at a time.  packed[8]: pooled bf16x2; am[4]: one argmax byte per channel
+// (0: this pixel, 1: next column, 2: next row, 3: diagonal; first maximum wins, like the scalar chain it replaces).
+template <int XW, int XH>
+__device__ __forceinline__ void pool2x2_bf16x16(const float (&v)[16], uint32_t (&packed)[8], uint32_t (&am)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) am[i] = 0u;
+#pragma unroll
+  for (int pi = 0; pi < 8; ++pi) {
+    const __nv_bfloat162 x = __floats2bfloat162_rn(v[2 * pi], v[2 * pi + 1]);
+    const uint32_t xu = *reinterpret_cast<const uint32_t*>(&x);
+    const uint32_t u01 = __shfl_xor_sync(0xffffffffu, xu, XW);
+    const uint32_t u10 = __shfl_xor_sync(0xffffffffu, xu, XH);
+    const uint32_t u11 = __shfl_xor_sync(0xffffffffu, xu, XW | XH);
+    const __nv_bfloat162 a01 = *reinterpret_cast<const __nv_bfloat162*>(&u01);
+    const __nv_bfloat162 a10 = *reinterpret_cast<const __nv_bfloat162*>(&u10);
+    const __nv_bfloat162 a11 = *reinterpret_cast<const __nv_bfloat162*>(&u11);
+    const __nv_bfloat162 best = __hmax2(__hmax2(x, a01), __hmax2(a10, a11));
+    const uint32_t e0 = __heq2_mask(x, best), e1 = __heq2_mask(a01, best), e2 = __heq2_mask(a10, best);
+    const uint32_t idx = ~e0 & ((e1 & 0x00010001u) | (~e1 & ((e2 & 0x00020002u) | (~e2 & 0x00030003u))));
+    packed[pi] = *reinterpret_cast<const uint32_t*>(&best);
+    am[pi >> 1] |= ((idx & 3u) | (((idx >> 16) & 3u) << 8)) << (16 * (pi & 1));
+  }
+}
+
+// 16-byte asynchronous global->shared copy (LDGSTS, bypassing L1) and its completion wait: the loader warps of the
+// smem-resident convolutions keep a whole image in flight without staging it through registers.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // ---------------------------------------------------------------- descriptors
 enum Swizzle : uint32_t { SW_NONE = 0, SW_128B = 2, SW_64B = 4, SW_32B = 6 };

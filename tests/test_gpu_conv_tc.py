@@ -10,11 +10,13 @@ from b200dp.ops import kernels as K
 bf16 = torch.bfloat16
 
 
-@pytest.fixture(params=["halo", "tma_shift"], autouse=True)
+@pytest.fixture(params=["halo", "resident", "tma_shift"], autouse=True)
 def conv_path(request, monkeypatch):
-    """Run every case through both tensor-core paths: the smem-resident persistent kernel (where the shape fits)
-    and the general shifted-TMA-box kernel."""
+    """Run every case through the three tensor-core paths: the smem-resident persistent kernel for small SAME images
+    (conv_halo.cu), the general smem-resident kernel (conv_res.cu) and the shifted-TMA-box kernel (conv_tc.cu).  Each
+    specialised kernel hands shapes it does not cover down the chain."""
     monkeypatch.setenv("B200DP_CONV_HALO", "1" if request.param == "halo" else "0")
+    monkeypatch.setenv("B200DP_CONV_RES", "0" if request.param == "tma_shift" else "1")
     return request.param
 
 
