@@ -37,6 +37,7 @@ def _check(res, np_, algo):
         assert d["int_sum"] == np_ * (np_ + 1) // 2
     r0 = res[0]
     assert r0["ckpt_step"] == 6
+    algo = algo.split("@")[0]
     if algo != "adasum":
         assert r0["oracle_cos"] > 0.9 and r0["adam_m_cos"] > 0.95, r0
     if algo in ("twoshot", "gemm_rs"):
@@ -45,13 +46,22 @@ def _check(res, np_, algo):
         assert r0["gemm_rs"] and 3 in r0["algos"], r0           # dense wgrad GEMM fused with its reduce-scatter
     if algo == "nvls" and r0.get("nvls_supported"):
         assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
-        assert r0["bcast_nvls"], r0                                   # and so did the large public broadcasts
+        assert r0["nvls_bcast_used"], r0                                   # and so did the large public broadcasts
 
 
 @pytest.mark.multigpu(2)
 @pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_two_gpus(tmp_path, algo):
     _check(_run(2, algo, tmp_path), 2, algo)
+
+
+@pytest.mark.multigpu(2)
+@pytest.mark.parametrize("algo", ["oneshot@keras128", "gemm_rs@keras128"])
+def test_two_gpus_keras128(tmp_path, algo):
+    """The keras128 family through the same fused allreduce+Adam / GEMM+reduce-scatter kernels (F=9216, D=128)."""
+    res = _run(2, algo, tmp_path)
+    assert res[0]["arch"] == "keras128"
+    _check(res, 2, algo)
 
 
 @pytest.mark.multigpu(4)

@@ -13,6 +13,9 @@ from b200dp.parallel.collectives import adasum_tree
 from b200dp.train.engine import TorchEngine
 
 out_dir, algo = sys.argv[1], sys.argv[2]
+arch = "mnist_cnn"
+if "@" in algo:                             # "<algo>@<arch>", e.g. gemm_rs@keras128
+    algo, arch = algo.split("@")
 if algo == "nvls":                         # also route large public broadcasts through the switch (multimem.st)
     os.environ["B200DP_BCAST"] = "nvls"
 if algo == "gemm_rs":                      # two-shot with the dense wgrad GEMM fused with its reduce-scatter
@@ -21,7 +24,7 @@ if algo == "gemm_rs":                      # two-shot with the dense wgrad GEMM 
 hvd.init(device="cuda")
 r, n = hvd.rank(), hvd.size()
 dev = hvd.device()
-res = {"rank": r, "size": n, "device": str(dev), "nccl_built": hvd.nccl_built()}
+res = {"rank": r, "size": n, "device": str(dev), "nccl_built": hvd.nccl_built(), "arch": arch}
 hvd.world().arena.set_timeout_ms(20000)
 
 
@@ -50,7 +53,7 @@ res["int_sum"] = int(ints[0])
 
 # ---- data-parallel training through the fused allreduce+Adam kernels --------------------------------
 B = 32
-spec = hvd.get_spec("mnist_cnn")
+spec = hvd.get_spec(arch)
 use_adasum = algo == "adasum"
 if algo == "nvls":
     res["nvls_supported"] = bool(hvd.world().arena.nvls_supported())
@@ -73,7 +76,7 @@ digests = hvd.allgather_object(digest)
 res["replicas_bitwise_identical"] = len(set(digests)) == 1
 res["sharded_ranges"] = len(eng._sharded_ranges)
 res["engine_nvls"] = bool(eng.nvls)
-res["bcast_nvls"] = bool(getattr(hvd.world().arena, "_staging_mc", False))
+res["nvls_bcast_used"] = bool(getattr(hvd.world().arena, "_staging_mc", False))
 res["gemm_rs"] = bool(eng.gemm_rs)
 res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
