@@ -119,9 +119,8 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
   pdl_launch_dependents();
-  // the bias is a weight written by the optimizer kernel: read it only after the dependency wait
-  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
-  __syncthreads();
+  // (the bias, a weight written by the optimizer kernel, is staged by the epilogue warps alone — see below — so the TMA,
+  // MMA and loader warps do not wait for that global round trip)
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -212,6 +211,8 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
     }
   } else {
     const int q = warp & 3;
+    for (int i = threadIdx.x - 64; i < p.N; i += 128) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+    asm volatile("bar.sync 1, 128;" ::: "memory");          // warps 2-5 only
     for (int it = 0; it < nimg; ++it) {
       const int img = blockIdx.x + it * gridDim.x;
       for (int tile = 0; tile < 2; ++tile) {

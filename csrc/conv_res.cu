@@ -13,7 +13,9 @@
 //
 // The image arrives in two halves (rows feeding the first 16 output rows, then the rest) on separate mbarriers, so the
 // first row of tiles starts while the second half is still in flight; accumulators rotate through a 4-deep TMEM ring so
-// the epilogue of one tile overlaps the MMAs of the next.
+// the epilogue of one tile overlaps the MMAs of the next.  The epilogue is the long pole of the forward (bias + ReLU + pool on
+// 64 channels), so it runs on EIGHT warps: the four dedicated ones take the lower half of the channels and the four loader
+// warps — idle once their image has landed, and sitting on the right TMEM lane quadrants (warp % 4) — take the upper half.
 //
 // Replaces cuDNN conv2d fwd/dgrad behind Keras Conv2D (horovod/tensorflow_mnist_gpu.py:47-56) — SURVEY K5/K6/K13.
 #include <stdlib.h>
@@ -51,9 +53,9 @@ struct ResParams {
 
 // TMEM lane r of the tile = output pixel (h0 + r/8, w0 + r%8); warp q owns lanes 32q..32q+31 = rows 4q..4q+3.
 __device__ __forceinline__ void res_epilogue(const ResParams& p, const float* sbias, uint32_t taddr, int img, int h0, int w0,
-                                             int lane, int q) {
+                                             int lane, int q, int c_begin, int c_end) {
   const int h = h0 + 4 * q + (lane >> 3), w = w0 + (lane & 7);
-  for (int c = 0; c < p.N; c += 16) {
+  for (int c = c_begin; c < c_end; c += 16) {
     uint32_t r[16];
     tmem_ld_32x16(taddr + c, r);
     tmem_ld_wait();
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
     for (int t = 0; t < ntaps; ++t) mbar_init(wfull + t, 1);
     for (int i = 0; i < 4; ++i) mbar_init(afull + i, 128);
     for (int i = 0; i < 2; ++i) mbar_init(aempty + i, 1);
-    for (int i = 0; i < NACC; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
+    for (int i = 0; i < NACC; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 8); }
     fence_barrier_init();
   }
   // Zero the image buffers once: the loader warps only ever write real pixels, so the margins stay zero for every image.
@@ -125,8 +127,8 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
   pdl_launch_dependents();
-  for (int i = threadIdx.x; i < p.N; i += blockDim.x) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
-  __syncthreads();
+  // channel split of the epilogue: [0, c_split) on warps 2-5, [c_split, N) on the loader warps 6-9
+  const int c_split = ((p.N / 16 + 1) / 2) * 16;
 
   if (warp == 0) {
     if (elect_one()) {
@@ -186,6 +188,7 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
     const int CK = p.Cred / 8;
     const int pieces = p.Hs * p.Ws * CK;
     const int split = min(p.hsplit, p.Hs) * p.Ws * CK;
+    int jl = 0;                                                    // running tile counter (accumulator ring slot), as in the MMA warp
     for (int it = 0; it < nimg; ++it) {
       const int buf = p.nbuf == 2 ? (it & 1) : 0;
       const uint32_t eph = ((uint32_t)(p.nbuf == 2 ? (it >> 1) : it) & 1u) ^ 1u;
@@ -205,16 +208,36 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
         }
         cp_async_commit();
       }
+      if (it == 0) {
+        // the bias is a weight written by the optimizer kernel (read after the dependency wait); only the eight epilogue
+        // warps need it, so only they meet on named barrier 1 — the TMA and MMA warps never wait for this round trip
+        for (int i = threadIdx.x - 64; i < p.N; i += 256) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+      }
       cp_async_wait_group<1>();
       fence_proxy_async();                   // generic-proxy writes -> visible to the tensor core's async proxy
       mbar_arrive(afull + buf * 2 + 0);
       cp_async_wait_group<0>();
       fence_proxy_async();
       mbar_arrive(afull + buf * 2 + 1);
+      if (it == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+      // second half of the epilogue of this image's tiles
+      const int q = warp & 3;
+      for (int tile = 0; tile < T; ++tile, ++jl) {
+        const int acc = jl % NACC;
+        mbar_wait(tfull + acc, ((uint32_t)(jl / NACC)) & 1u, 36);
+        tc_fence_after();
+        if (!(p.dbg & 8)) res_epilogue(p, sbias, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.N), img, (tile / p.TW) * 16,
+                                       (tile % p.TW) * 8, lane, q, c_split, p.N);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty + acc);
+      }
     }
   } else {
     const int q = warp & 3;
     int j = 0;
+    for (int i = threadIdx.x - 64; i < p.N; i += 256) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     for (int it = 0; it < nimg; ++it) {
       const int img = blockIdx.x + it * gridDim.x;
       for (int tile = 0; tile < T; ++tile, ++j) {
@@ -222,7 +245,7 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
         mbar_wait(tfull + acc, ((uint32_t)(j / NACC)) & 1u, 35);
         tc_fence_after();
         if (!(p.dbg & 8)) res_epilogue(p, sbias, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.N), img, (tile / p.TW) * 16,
-                     (tile % p.TW) * 8, lane, q);
+                                       (tile % p.TW) * 8, lane, q, 0, c_split);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty + acc);
