@@ -188,8 +188,7 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
     const int CK = p.Cred / 8;
     const int pieces = p.Hs * p.Ws * CK;
     const int split = min(p.hsplit, p.Hs) * p.Ws * CK;
-    int jl = 0;                                                    // running tile counter (accumulator ring slot), as in the MMA warp
-    for (int it = 0; it < nimg; ++it) {
+    auto load_image = [&](int it) {
       const int buf = p.nbuf == 2 ? (it & 1) : 0;
       const uint32_t eph = ((uint32_t)(p.nbuf == 2 ? (it >> 1) : it) & 1u) ^ 1u;
       mbar_wait(aempty + buf, eph, 31);
@@ -208,20 +207,27 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
         }
         cp_async_commit();
       }
-      if (it == 0) {
-        // the bias is a weight written by the optimizer kernel (read after the dependency wait); only the eight epilogue
-        // warps need it, so only they meet on named barrier 1 — the TMA and MMA warps never wait for this round trip
-        for (int i = threadIdx.x - 64; i < p.N; i += 256) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
-      }
       cp_async_wait_group<1>();
       fence_proxy_async();                   // generic-proxy writes -> visible to the tensor core's async proxy
       mbar_arrive(afull + buf * 2 + 0);
       cp_async_wait_group<0>();
       fence_proxy_async();
       mbar_arrive(afull + buf * 2 + 1);
-      if (it == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
-      // second half of the epilogue of this image's tiles
-      const int q = warp & 3;
+    };
+    load_image(0);
+    // the bias is a weight written by the optimizer kernel (read after the dependency wait); only the eight epilogue
+    // warps need it, so only they meet on named barrier 1 — the TMA and MMA warps never wait for this round trip
+    for (int i = threadIdx.x - 64; i < p.N; i += 256) sbias[i] = p.bias ? __bfloat162float(p.bias[i]) : 0.f;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const int q = warp & 3;
+    int jl = 0;                                                    // running tile counter (accumulator ring slot), as in the MMA warp
+    for (int it = 0; it < nimg; ++it) {
+      // With two buffers the next image is fetched first: its buffer was freed by the MMAs of image it-1, which never wait
+      // on this warp's pending work.  With one buffer the fetch needs image `it` fully consumed, and those MMAs wait on
+      // the accumulator slots this warp is about to release, so the epilogue has to come first.
+      if (p.nbuf == 2 && it + 1 < nimg) load_image(it + 1);
+      const int img = blockIdx.x + it * gridDim.x;
+      // upper half of the channels of this image's tiles
       for (int tile = 0; tile < T; ++tile, ++jl) {
         const int acc = jl % NACC;
         mbar_wait(tfull + acc, ((uint32_t)(jl / NACC)) & 1u, 36);
@@ -232,6 +238,7 @@ __global__ void __launch_bounds__(320, 1) conv_res_kernel(const __grid_constant_
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty + acc);
       }
+      if (p.nbuf != 2 && it + 1 < nimg) load_image(it + 1);
     }
   } else {
     const int q = warp & 3;
