@@ -27,11 +27,18 @@ class ReduceOp(enum.Enum):
     Average = "average"
     Sum = "sum"
     Adasum = "adasum"
+    Min = "min"
+    Max = "max"
+    Product = "product"
 
 
 Average = ReduceOp.Average
 Sum = ReduceOp.Sum
 Adasum = ReduceOp.Adasum
+Min = ReduceOp.Min
+Max = ReduceOp.Max
+Product = ReduceOp.Product
+_ORDER_OPS = {ReduceOp.Min: dist.ReduceOp.MIN, ReduceOp.Max: dist.ReduceOp.MAX, ReduceOp.Product: dist.ReduceOp.PRODUCT}
 
 
 def _is_pow2(n: int) -> bool:
@@ -74,6 +81,11 @@ def _cpu_allreduce_(t: torch.Tensor, op: ReduceOp) -> torch.Tensor:
         t.copy_(adasum_tree(parts))
         return t
     work = t if t.is_contiguous() else t.contiguous()
+    if op in _ORDER_OPS:
+        acc = work.float() if work.dtype in (torch.bfloat16, torch.float16) else work
+        dist.all_reduce(acc, op=_ORDER_OPS[op])
+        t.copy_(acc.to(t.dtype))
+        return t
     if work.dtype in (torch.bfloat16, torch.float16):
         acc = work.float()
         dist.all_reduce(acc, op=dist.ReduceOp.SUM)
@@ -98,6 +110,13 @@ def allreduce_(tensor: torch.Tensor, op: ReduceOp = Average, name: Optional[str]
     inside a fused buffer so Adasum computes its dot products per tensor."""
     w = _w.world()
     if w.size == 1:
+        return tensor
+    if tensor.is_cuda and op in _ORDER_OPS:
+        # Min / Max / Product are metric-sized in practice: they ride the control plane (the NVLink kernels implement the
+        # gradient reductions: sum, average, Adasum)
+        host = tensor.detach().cpu()
+        _cpu_allreduce_(host, op)
+        tensor.copy_(host.to(tensor.device))
         return tensor
     if tensor.is_cuda:
         if w.arena is None:

@@ -81,9 +81,10 @@ class _DistributedTorchOptimizer:
     """
 
     def __init__(self, optimizer: torch.optim.Optimizer, named_parameters=None, op: C.ReduceOp = C.Average,
-                 bucket_bytes: Optional[int] = None, backward_passes_per_step: int = 1):
+                 bucket_bytes: Optional[int] = None, backward_passes_per_step: int = 1, compression=None):
         self._opt = optimizer
         self.op = op
+        self._compression = compression
         params: List[torch.nn.Parameter] = []
         for g in optimizer.param_groups:
             params.extend(p for p in g["params"] if p.requires_grad)
@@ -157,6 +158,15 @@ class _DistributedTorchOptimizer:
         if self._passes > 1:
             flat /= self._passes
         work = None
+        ctx = None
+        if self._compression is not None:
+            # Horovod's `compression=`: the bucket is rounded to the wire type before the reduction and widened after it
+            wire, ctx = self._compression.compress(flat)
+            if ctx is not None:
+                C.allreduce_(wire, self.op, segments=[p.numel() for p in ps])
+                flat = self._compression.decompress(wire, ctx)
+                self._pending[bi] = (None, flat, ps)
+                return
         if dev.type == "cpu" and self.op in (C.Average, C.Sum):
             import torch.distributed as dist
             work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, async_op=True)
@@ -197,7 +207,7 @@ class _DistributedTorchOptimizer:
 
 def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Average, *,
                          algo: str = "auto", bucket_bytes: Optional[int] = None,
-                         backward_passes_per_step: int = 1):
+                         backward_passes_per_step: int = 1, compression=None):
     """Horovod-named factory (see module docstring)."""
     if isinstance(optimizer, DistributedAdam):
         return optimizer
@@ -205,5 +215,5 @@ def DistributedOptimizer(optimizer, named_parameters=None, op: C.ReduceOp = C.Av
         algo = os.environ.get("B200DP_ALLREDUCE_ALGO", algo)
         return DistributedAdam(base=optimizer, op=op, algo=algo)
     if isinstance(optimizer, torch.optim.Optimizer):
-        return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes, backward_passes_per_step)
+        return _DistributedTorchOptimizer(optimizer, named_parameters, op, bucket_bytes, backward_passes_per_step, compression)
     raise TypeError(f"cannot wrap optimizer of type {type(optimizer).__name__}")

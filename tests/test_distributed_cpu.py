@@ -32,6 +32,10 @@ def test_collectives(tmp_path, np_):
             assert d[k], (i, k)
         assert d["obj"] == 0 and d["gather"] == list(range(np_))
         assert d["bf16_avg"] == pytest.approx((np_ - 1) / 2)
+        for k in ("async_avg_ok", "async_bcast_ok", "grouped_ok", "grouped_adasum_ok", "alltoall_ok", "alltoall_even_ok",
+                  "reducescatter_ok", "minmax_ok", "compression_ok"):
+            assert d[k], (i, k)
+        assert 0 <= d["join"] < np_ and d["cross"] == [0, 1]
 
 
 def _example(name, tmp_path, np_, args, env=None, extra=()):
@@ -93,3 +97,54 @@ def test_killed_rank_fails_job_then_restart_resumes(tmp_path):
     # first attempt restores (>= step 6), dies again only if it passes step 7 at restart 0; either way ends clean
     assert r2.returncode == 0, r2.stderr[-3000:]
     assert "ckpt-20.safetensors" in os.listdir(ck)
+
+
+def test_elastic_state_resumes_from_last_commit_after_a_rank_dies(tmp_path):
+    """hvd.elastic on top of the restart supervisor: rank 1 dies at batch 6 (last commit: 4); the relaunched job syncs the
+    persisted commit from rank 0, runs the reset callbacks and finishes; replicas end bitwise identical."""
+    r = _launch(2, [os.path.join(W, "elastic_worker.py"), str(tmp_path), "1", "6"], extra=["--max-restarts", "1", "--grace-secs", "2"])
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "restart 1/1" in r.stderr
+    res = [json.load(open(p)) for p in sorted(glob.glob(str(tmp_path / "r*.json")))]
+    assert len(res) == 2
+    for d in res:
+        assert d["restart"] == 1 and d["first_batch"] == 4 and d["final_batch"] == 12
+        assert d["seen"] == list(range(12))                  # batches 4 and 5 were replayed, nothing skipped
+        assert d["global_step"] == 12 and d["resets"] == [1]
+        assert d["commits"] == 3                             # 4 (persisted before the failure), 8, 12
+    assert res[0]["digest"] == res[1]["digest"]
+    recs = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert any(d.get("event") == "elastic_resume" and d.get("commits") == 1 for d in recs)
+
+
+def test_elastic_state_single_process_commit_restore(tmp_path):
+    import torch
+    import b200dp as hvd
+    lin = torch.nn.Linear(3, 2)
+    opt = torch.optim.SGD(lin.parameters(), lr=0.1, momentum=0.9)
+    st = hvd.elastic.TorchState(lin, opt, directory=str(tmp_path), epoch=0, best=1e9)
+    lin(torch.ones(1, 3)).sum().backward(); opt.step()
+    st.epoch, st.best = 2, 0.5
+    st.commit()
+    w_commit = lin.weight.detach().clone()
+    lin(torch.ones(1, 3)).sum().backward(); opt.step()
+    st.epoch = 3
+    assert not torch.equal(lin.weight, w_commit)
+    st.restore()
+    assert st.epoch == 2 and st.best == 0.5 and torch.equal(lin.weight, w_commit)
+    # a fresh process adopts the persisted commit
+    lin2 = torch.nn.Linear(3, 2)
+    st2 = hvd.elastic.TorchState(lin2, torch.optim.SGD(lin2.parameters(), lr=0.1, momentum=0.9), directory=str(tmp_path), epoch=0, best=1e9)
+    assert st2.load_persisted() and st2.epoch == 2 and st2.commits == 1 and torch.equal(lin2.weight, w_commit)
+    # resize request at a commit point
+    flag = tmp_path / "resize"
+    flag.write_text("4")
+    os.environ["B200DP_RESIZE_FILE"] = str(flag)
+    try:
+        with pytest.raises(hvd.elastic.HostsUpdatedInterrupt):
+            st.commit()
+        with pytest.raises(SystemExit) as ei:
+            hvd.elastic.run(lambda s: s.commit())(st)
+        assert ei.value.code == 75
+    finally:
+        del os.environ["B200DP_RESIZE_FILE"]

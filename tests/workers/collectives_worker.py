@@ -61,5 +61,42 @@ for rr in range(n):
     for k in range(2):
         exp += torch.randn(3, 4, generator=torch.Generator().manual_seed(50 + 10 * k + rr)).sum(0).expand(2, 4)
 res["accumulation_ok"] = bool(torch.allclose(w0 - lin2.weight.detach(), exp / (2 * n), atol=1e-5))
+
+# ---- the rest of Horovod's collective API (b200dp/parallel/extras.py) ----------------------------------------------
+h = hvd.allreduce_async(t, op=hvd.Average)
+h2 = hvd.broadcast_async(torch.full((5,), float(r)), root_rank=0)
+res["async_avg_ok"] = bool(torch.allclose(hvd.synchronize(h), torch.stack(all_t).mean(0), atol=1e-6)) and hvd.poll(h)
+res["async_bcast_ok"] = bool(torch.equal(hvd.synchronize(h2), torch.zeros(5)))
+a, b2 = torch.full((3,), float(r + 1)), torch.full((2, 2), float(10 * (r + 1)), dtype=torch.float64)
+ga, gb = hvd.grouped_allreduce([a, b2], op=hvd.Sum)
+tot = n * (n + 1) / 2
+res["grouped_ok"] = bool(torch.allclose(ga, torch.full((3,), tot)) and torch.allclose(gb, torch.full((2, 2), 10 * tot, dtype=torch.float64))
+                         and gb.dtype == torch.float64 and torch.equal(a, torch.full((3,), float(r + 1))))
+gad = hvd.grouped_allreduce([all_t[r][:100].clone(), all_t[r][100:300].clone()], op=hvd.Adasum)
+res["grouped_adasum_ok"] = bool(torch.allclose(gad[0], adasum_tree([x[:100] for x in all_t]), atol=1e-5)
+                                and torch.allclose(gad[1], adasum_tree([x[100:300] for x in all_t]), atol=1e-5))
+# alltoall: rank r sends (dst + 1) rows tagged 100*r + dst to every dst
+send = torch.cat([torch.full((d + 1, 2), float(100 * r + d)) for d in range(n)])
+got, counts = hvd.alltoall(send, splits=[d + 1 for d in range(n)])
+exp_rows = torch.cat([torch.full((r + 1, 2), float(100 * src + r)) for src in range(n)])
+res["alltoall_ok"] = bool(torch.equal(got, exp_rows)) and counts == [r + 1] * n
+even = hvd.alltoall(torch.arange(2 * n, dtype=torch.float32) + 1000 * r)
+res["alltoall_even_ok"] = bool(torch.equal(even, torch.cat([torch.arange(2 * r, 2 * r + 2, dtype=torch.float32) + 1000 * src for src in range(n)])))
+rs = hvd.reducescatter(torch.arange(2 * n + 1, dtype=torch.float32) * (r + 1), op=hvd.Sum)
+full = torch.arange(2 * n + 1, dtype=torch.float32) * tot
+lo = r * 2 + min(r, 1)
+res["reducescatter_ok"] = bool(torch.equal(rs, full[lo:lo + 2 + (1 if r < 1 else 0)]))
+res["minmax_ok"] = (float(hvd.allreduce(torch.tensor([float(r)]), op=hvd.Max)) == n - 1 and float(hvd.allreduce(torch.tensor([float(r)]), op=hvd.Min)) == 0.0
+                    and int(hvd.allreduce(torch.tensor([2]), op=hvd.Product)) == 2 ** n)
+res["join"] = hvd.join()
+res["cross"] = [hvd.cross_rank(), hvd.cross_size()]
+# wire compression: gradients rounded to fp16 for the reduction, replicas still identical
+lin3 = torch.nn.Linear(5, 2)
+hvd.broadcast_parameters(lin3.state_dict(), 0)
+opt3 = hvd.DistributedOptimizer(torch.optim.SGD(lin3.parameters(), lr=0.5), compression=hvd.Compression.fp16)
+lin3(torch.randn(4, 5, generator=torch.Generator().manual_seed(77 + r))).pow(2).sum().backward()
+opt3.step()
+f3 = torch.cat([p.detach().flatten() for p in lin3.parameters()])
+res["compression_ok"] = bool(torch.equal(f3, hvd.broadcast(f3, 0))) and lin3.weight.grad.dtype == torch.float32
 json.dump(res, open(os.path.join(out_dir, f"r{r}.json"), "w"))
 hvd.shutdown()
