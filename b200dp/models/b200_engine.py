@@ -189,6 +189,13 @@ class B200Engine(Engine):
         self.dist: Optional[DistributedAdam] = None
         self.adam: Optional[Adam] = None
         self.set_optimizer(optimizer)
+        if _env_flag("B200DP_L2_PERSIST", "0"):
+            # experiment: pin the fp32 master/m/v sweep target in L2 for the streams the fused Adam kernels run on
+            # (the dense bucket's kernel runs on comm_stream; a graph capture gives the main chain a stream of its own)
+            for st in [s for s in (torch.cuda.current_stream(), self.comm_stream) if s.cuda_stream != 0]:
+                K.check(K.lib().b200_stream_l2_persist(ctypes.c_void_p(self.master.data_ptr()), T * 4 * 3,
+                                                       float(os.environ.get("B200DP_L2_PERSIST_RATIO", "1.0")),
+                                                       ctypes.c_void_p(st.cuda_stream)), "l2_persist")
         torch.cuda.synchronize()
 
     @property

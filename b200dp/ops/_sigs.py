@@ -64,6 +64,7 @@ _SIGS = {
     "b200_conv_tc_wgrad_pad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
     "b200_topology_json": (I, [C.c_char_p, I]),
     "b200_l2_flush": (I, [P, SZ, P]),
+    "b200_stream_l2_persist": (I, [P, SZ, F, P]),
     "b200_set_pdl": (I, [I]),
 }
 

@@ -179,6 +179,9 @@ int b200_conv_tc_wgrad_pad(const void* in, const void* dout, float* dw, float* d
 /* JSON description of the visible GPUs: names, SM counts, memory, peer-access matrix. Returns bytes written. */
 int b200_topology_json(char* buf, int buflen);
 int b200_l2_flush(void* scratch, size_t bytes, void* stream);
+/* L2 access-policy window on a stream (persisting hits, streaming misses); bytes == 0 clears it.  Opt-in experiment of the
+ * engine (B200DP_L2_PERSIST=1): keep the Adam state resident between steps. */
+int b200_stream_l2_persist(void* base, size_t bytes, float hit_ratio, void* stream);
 /* Programmatic dependent launch for the step kernels (default on; also B200DP_PDL=0). */
 int b200_set_pdl(int on);
 
