@@ -23,7 +23,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from typing import Any, Dict, List, Optional, Tuple, Union
+from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
 import torch

@@ -13,8 +13,6 @@ hooks (reference: ``horovod/tensorflow_mnist.py:133,143``;
 from __future__ import annotations
 
 import enum
-import io
-import pickle
 from typing import Any, Iterable, List, Optional
 
 import torch

@@ -8,8 +8,7 @@ reducescatter, ``join`` and wire compression; they are provided here on top of t
 """
 from __future__ import annotations
 
-import threading
-from typing import Any, Callable, Dict, List, Optional, Sequence
+from typing import Any, Callable, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist

@@ -17,7 +17,7 @@ from __future__ import annotations
 
 import os
 from dataclasses import dataclass, replace
-from typing import Iterable, List, Optional, Tuple
+from typing import List, Optional
 
 import torch
 

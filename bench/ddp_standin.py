@@ -3,7 +3,6 @@
 over NCCL, bf16 autocast, channels-last, fused Adam.  "A path that only calls NCCL" — the baseline."""
 import json
 import os
-import time
 
 import torch
 import torch.distributed as dist

@@ -1,6 +1,4 @@
 """CUDA-core kernels vs plain PyTorch fp32 references (SURVEY §4.3 'Kernel (GPU)')."""
-import math
-
 import pytest
 import torch
 import torch.nn.functional as F

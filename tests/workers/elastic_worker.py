@@ -36,7 +36,7 @@ def train(state):
 
 
 first = train(state)
-import hashlib, torch
+import hashlib
 digest = hashlib.sha256(eng.params.data.numpy().tobytes()).hexdigest()
 json.dump({"rank": r, "restart": restart, "first_batch": first, "final_batch": state.batch, "seen": state.seen, "commits": state.commits,
            "global_step": eng.global_step, "resets": resets, "digest": digest}, open(os.path.join(out_dir, f"r{r}.json"), "w"))

@@ -3,7 +3,7 @@
     python tools/step_timeline.py [--batch 128] [--steps 20] [--out gpurun_out/timeline]"""
 import argparse, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
+import torch
 import b200dp as hvd
 from b200dp.utils.timeline import Timeline
 
