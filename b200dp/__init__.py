@@ -18,7 +18,7 @@ from .parallel.extras import (Handle, poll, synchronize, allreduce_async, allred
                               ccl_built, ddl_built, cross_rank, cross_size)
 from .parallel.optimizer import Adam, DistributedAdam, DistributedOptimizer, lr_scaler
 from .train.session import (MonitoredTrainingSession, SessionRunHook, BroadcastGlobalVariablesHook,
-                            StopAtStepHook, LoggingTensorHook, StepCounterHook, CheckpointSaverHook)
+                            StopAtStepHook, LoggingTensorHook, StepCounterHook, CheckpointSaverHook, MetricsHook)
 from .train.trainer import Model, MNISTModel, SparseCategoricalCrossentropy
 from .train.engine import make_engine, TorchEngine, StepResult
 from .models.spec import get_spec

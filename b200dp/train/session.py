@@ -104,15 +104,37 @@ class CheckpointSaverHook(SessionRunHook):
     def __init__(self, manager: CheckpointManager):
         self.manager = manager
 
+    @staticmethod
+    def _count(session) -> None:
+        if session.metrics is not None:
+            session.metrics.checkpoints.inc()
+
     def after_run(self, session, result):
         p = self.manager.maybe_save(session.engine.state, session.engine.global_step)
         if p:
             get_logger().info("checkpoint_saved", path=p, step=session.engine.global_step)
+            self._count(session)
 
     def end(self, session):
         if self.manager.enabled:
             p = self.manager.save(session.engine.state(), session.engine.global_step)
             get_logger().info("checkpoint_saved", path=p, step=session.engine.global_step, final=True)
+            self._count(session)
+
+
+class MetricsHook(SessionRunHook):
+    """Feeds the Prometheus exporter (:mod:`b200dp.utils.metrics`) every ``every_n_iter`` iterations — the cadence at
+    which the loss is read back anyway, so the exporter adds no device synchronisation of its own."""
+
+    def __init__(self, exporter, every_n_iter: int = 10):
+        self.exporter = exporter
+        self.every = max(1, every_n_iter)
+        self._iter = 0
+
+    def after_run(self, session, result):
+        if self._iter % self.every == 0:
+            self.exporter.observe_step(session.engine.global_step, result.n, loss=result.loss_value(), accuracy=result.accuracy())
+        self._iter += 1
 
 
 class FaultInjectionHook(SessionRunHook):
@@ -151,6 +173,12 @@ class MonitoredTrainingSession:
             if log_step_count_steps:
                 self.hooks.append(StepCounterHook(log_step_count_steps))
         self.hooks.append(FaultInjectionHook())
+        # B200DP_METRICS_PORT=<port>: a Prometheus /metrics endpoint per rank (port + local_rank)
+        from ..utils.metrics import exporter_from_env
+        me = (_w.rank(), _w.size(), _w.local_rank()) if _w.is_initialized() else (0, 1, 0)
+        self.metrics = exporter_from_env(*me)
+        if self.metrics is not None and not any(isinstance(h, MetricsHook) for h in self.hooks):
+            self.hooks.append(MetricsHook(self.metrics))
         self._stop = False
         self._entered = False
         self.last_result: Optional[StepResult] = None

@@ -146,6 +146,26 @@ class History(Callback):
             self.history.setdefault(k, []).append(v)
 
 
+class MetricsCallback(Callback):
+    """Feeds the Prometheus exporter (:mod:`b200dp.utils.metrics`) every ``every_n_batches`` batches and at epoch end."""
+
+    def __init__(self, exporter, every_n_batches: int = 50):
+        self.exporter = exporter
+        self.every = max(1, every_n_batches)
+        self._n = 0
+
+    def on_train_batch_end(self, batch, logs=None):
+        self._n += 1
+        if self._n % self.every == 0:
+            eng = self.model.engine
+            self.exporter.observe_step(eng.global_step, getattr(self.model, "_last_batch", 0) or 0)
+
+    def on_epoch_end(self, epoch, logs=None):
+        eng = self.model.engine
+        self.exporter.observe_step(eng.global_step, getattr(self.model, "_last_batch", 0) or 0,
+                                   loss=(logs or {}).get("loss"), accuracy=(logs or {}).get("accuracy"))
+
+
 class FaultInjectionCallback(Callback):
     def on_train_batch_end(self, batch, logs=None):
         spec = os.environ.get("B200DP_FAULT", "")
@@ -210,6 +230,11 @@ class Model:
             steps_per_epoch = max(1, n // batch_size)
         hist = History()
         cbs: List[Callback] = list(callbacks or []) + [hist, FaultInjectionCallback()]
+        from ..utils.metrics import exporter_from_env
+        exp = exporter_from_env(_w.rank(), _w.size(), _w.local_rank()) if _w.is_initialized() else exporter_from_env(0, 1, 0)
+        if exp is not None and not any(isinstance(c, MetricsCallback) for c in cbs):
+            cbs.append(MetricsCallback(exp))
+        self._last_batch = batch_size
         for cb in cbs:
             cb.set_model(self)
         for cb in cbs:

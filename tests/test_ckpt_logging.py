@@ -137,3 +137,29 @@ def test_keras128_falls_back_to_torch_engine():
     eng = hvd.make_engine(hvd.get_spec("keras128", 0.25), hvd.Adam(1e-3), engine="torch")
     r = eng.train_step(np.random.rand(4, 784).astype(np.float32), np.array([1, 2, 3, 4]))
     assert np.isfinite(r.loss_value())
+
+
+def test_prometheus_exporter_serves_step_metrics(tmp_path):
+    """the reference defines no Prometheus metrics; ours are optional and served per rank."""
+    import urllib.request
+    import b200dp as hvd
+    from b200dp.utils.metrics import MetricsExporter
+    exp = MetricsExporter(rank=0, size=2)
+    port = exp.serve(0, addr="127.0.0.1")
+    try:
+        eng = hvd.make_engine(hvd.get_spec("mnist_cnn", 0.25), hvd.Adam(1e-3), engine="torch")
+        x, y = np.random.rand(8, 784).astype(np.float32), np.arange(8) % 10
+        hooks = [hvd.StopAtStepHook(last_step=6), hvd.MetricsHook(exp, every_n_iter=2)]
+        with hvd.MonitoredTrainingSession(eng, checkpoint_dir=str(tmp_path), hooks=hooks, save_checkpoint_secs=None) as sess:
+            sess.metrics = exp
+            while not sess.should_stop():
+                sess.run(x, y)
+        body = urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics", timeout=5).read().decode()
+    finally:
+        exp.close()
+    vals = {l.split("{")[0]: float(l.rsplit(" ", 1)[1]) for l in body.splitlines() if l.startswith("b200dp_") and "{" in l}
+    assert vals["b200dp_global_step"] == 5.0                       # sampled at iterations 0, 2, 4 -> steps 1, 3, 5
+    assert vals["b200dp_steps_total"] == 4.0 and vals["b200dp_world_size"] == 2.0
+    assert vals["b200dp_images_per_second"] > 0 and vals["b200dp_step_seconds"] > 0
+    assert np.isfinite(vals["b200dp_loss"]) and vals["b200dp_checkpoints_total"] == 1.0      # the final save
+    assert 'rank="0"' in body and vals["b200dp_last_step_timestamp_seconds"] > 1.6e9
