@@ -30,6 +30,13 @@ helm upgrade --install loki grafana/loki-stack \
   -f "$HERE/promtail-pipeline.yaml" \
   --wait
 
+# Grafana's dashboard sidecar (enabled in the chart by default) loads every ConfigMap labelled grafana_dashboard=1
+kubectl create configmap b200dp-dashboard -n "$LOKI_NAMESPACE" --from-file=b200dp.json="$HERE/grafana-dashboard.json" \
+  --dry-run=client -o yaml | kubectl label --local -f - grafana_dashboard=1 -o yaml | kubectl apply -f -
+# alert rules for the Loki ruler (stall, rank error, restart, straggler)
+kubectl create configmap b200dp-loki-rules -n "$LOKI_NAMESPACE" --from-file=b200dp-rules.yaml="$HERE/loki-rules.yaml" \
+  --dry-run=client -o yaml | kubectl apply -f -
+
 echo "[3/4] kubeflow MPI Operator (v2beta1)"
 kubectl apply --server-side -f "$MPI_OPERATOR_MANIFEST"
 

@@ -55,3 +55,33 @@ def test_deploy_script_and_dockerfile():
         assert needle in sh
     df = open(os.path.join(D, "Dockerfile")).read()
     assert "tools/build.py" in df and "openssh-server" in df and "/examples/tensorflow_mnist.py" in df
+
+
+def test_grafana_dashboard_and_loki_rules_use_events_the_framework_emits():
+    """Every LogQL selector in the dashboard / alert rules names an event that some b200dp module really logs."""
+    import json
+    import re
+    root = os.path.dirname(D)
+    emitted = set()
+    for dp, _, fns in os.walk(os.path.join(root, "b200dp")):
+        for fn in fns:
+            if fn.endswith(".py"):
+                emitted |= set(re.findall(r'(?:info|warning|error|log)\("([a-z_]+)"', open(os.path.join(dp, fn)).read()))
+    dash = json.load(open(os.path.join(D, "grafana-dashboard.json")))
+    exprs = [t["expr"] for p in dash["panels"] for t in p["targets"]]
+    assert len(dash["panels"]) >= 6 and dash["uid"] == "b200dp-train"
+    rules = yaml.safe_load(open(os.path.join(D, "loki-rules.yaml")))
+    alerts = rules["groups"][0]["rules"]
+    assert {a["alert"] for a in alerts} >= {"B200dpTrainingStalled", "B200dpRankError", "B200dpJobRestarted", "B200dpStragglerRank"}
+    exprs += [a["expr"] for a in alerts]
+    used = set()
+    for e in exprs:
+        for m in re.findall(r'event=~?"([^"]+)"', e):
+            used |= {x for x in m.split("|") if re.fullmatch(r"[a-z_]+", x)}
+    assert used and used <= emitted, used - emitted
+    sh = open(os.path.join(D, "deploy_stack.sh")).read()
+    assert "grafana-dashboard.json" in sh and "grafana_dashboard=1" in sh and "loki-rules.yaml" in sh
+    j = yaml.safe_load(open(os.path.join(D, "b200dp-mnist.yaml")))
+    w = j["spec"]["mpiReplicaSpecs"]["Worker"]["template"]
+    assert w["metadata"]["annotations"]["prometheus.io/port"] == "9400"
+    assert "B200DP_METRICS_PORT=9400" in j["spec"]["mpiReplicaSpecs"]["Launcher"]["template"]["spec"]["containers"][0]["args"]
