@@ -157,14 +157,29 @@ def broadcast(tensor: torch.Tensor, root_rank: int = 0, name: Optional[str] = No
 
 
 def allgather(tensor: torch.Tensor, name: Optional[str] = None) -> torch.Tensor:
-    """Concatenate along dim 0 across ranks (equal shapes)."""
+    """Concatenate along dim 0 across ranks.  Dim 0 may differ per rank (Horovod's allgather allows it); the other
+    dimensions must agree."""
     w = _w.world()
     if w.size == 1:
         return tensor.clone()
     cpu = tensor.detach().cpu().contiguous()
-    parts = [torch.empty_like(cpu) for _ in range(w.size)]
-    dist.all_gather(parts, cpu)
-    return torch.cat(parts, dim=0).to(tensor.device)
+    if cpu.dim() == 0:
+        cpu = cpu.reshape(1)
+    shapes = allgather_object(tuple(cpu.shape))
+    if any(sh[1:] != shapes[0][1:] for sh in shapes):
+        raise ValueError(f"allgather: trailing dimensions differ across ranks: {shapes}")
+    rows = [sh[0] for sh in shapes]
+    if len(set(rows)) == 1:
+        parts = [torch.empty_like(cpu) for _ in range(w.size)]
+        dist.all_gather(parts, cpu)
+        return torch.cat(parts, dim=0).to(tensor.device)
+    # ragged: pad every contribution to the longest, gather, trim
+    top = max(rows)
+    padded = torch.zeros((top,) + tuple(cpu.shape[1:]), dtype=cpu.dtype)
+    padded[:cpu.shape[0]] = cpu
+    parts = [torch.empty_like(padded) for _ in range(w.size)]
+    dist.all_gather(parts, padded)
+    return torch.cat([p[:r] for p, r in zip(parts, rows)], dim=0).to(tensor.device)
 
 
 def broadcast_object(obj: Any, root_rank: int = 0) -> Any:

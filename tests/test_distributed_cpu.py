@@ -33,7 +33,7 @@ def test_collectives(tmp_path, np_):
         assert d["obj"] == 0 and d["gather"] == list(range(np_))
         assert d["bf16_avg"] == pytest.approx((np_ - 1) / 2)
         for k in ("async_avg_ok", "async_bcast_ok", "grouped_ok", "grouped_adasum_ok", "alltoall_ok", "alltoall_even_ok",
-                  "reducescatter_ok", "minmax_ok", "compression_ok"):
+                  "reducescatter_ok", "minmax_ok", "compression_ok", "ragged_gather_ok"):
             assert d[k], (i, k)
         assert 0 <= d["join"] < np_ and d["cross"] == [0, 1]
 

@@ -88,6 +88,8 @@ lo = r * 2 + min(r, 1)
 res["reducescatter_ok"] = bool(torch.equal(rs, full[lo:lo + 2 + (1 if r < 1 else 0)]))
 res["minmax_ok"] = (float(hvd.allreduce(torch.tensor([float(r)]), op=hvd.Max)) == n - 1 and float(hvd.allreduce(torch.tensor([float(r)]), op=hvd.Min)) == 0.0
                     and int(hvd.allreduce(torch.tensor([2]), op=hvd.Product)) == 2 ** n)
+rag = hvd.allgather(torch.full((r + 1, 2), float(r)))
+res["ragged_gather_ok"] = bool(torch.equal(rag, torch.cat([torch.full((i + 1, 2), float(i)) for i in range(n)])))
 res["join"] = hvd.join()
 res["cross"] = [hvd.cross_rank(), hvd.cross_size()]
 # wire compression: gradients rounded to fp16 for the reduction, replicas still identical
