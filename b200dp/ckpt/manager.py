@@ -142,11 +142,24 @@ class CheckpointManager:
                     pass
 
     def restore(self) -> Optional[Dict[str, Any]]:
-        p = self.latest()
-        if p is None:
+        """Load the newest checkpoint that can be read.  Writes are atomic, so a half-written file never carries the
+        final name; this guards against the rest (bit rot or truncation on shared storage): an unreadable checkpoint is
+        reported and the next older one is tried, so one bad file costs ``save_secs`` of work instead of the run."""
+        first = self.latest()
+        if first is None:
             return None
-        tensors, meta = load_tensors(p)
-        return {"tensors": tensors, "meta": meta, "path": p}
+        candidates = [first] + [p for _, p in reversed(self.list()) if p != first]
+        last_err: Optional[Exception] = None
+        for p in candidates:
+            try:
+                tensors, meta = load_tensors(p)
+            except Exception as e:                     # safetensors raises several types for damaged files
+                last_err = e
+                from ..utils.logging import get_logger
+                get_logger().warning("checkpoint_unreadable", path=p, error=repr(e))
+                continue
+            return {"tensors": tensors, "meta": meta, "path": p}
+        raise RuntimeError(f"no readable checkpoint in {self.dir}: {last_err!r}")
 
     def due(self, step: int) -> bool:
         if not self.enabled or self._last_save_step == step:

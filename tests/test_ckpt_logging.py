@@ -163,3 +163,20 @@ def test_prometheus_exporter_serves_step_metrics(tmp_path):
     assert vals["b200dp_images_per_second"] > 0 and vals["b200dp_step_seconds"] > 0
     assert np.isfinite(vals["b200dp_loss"]) and vals["b200dp_checkpoints_total"] == 1.0      # the final save
     assert 'rank="0"' in body and vals["b200dp_last_step_timestamp_seconds"] > 1.6e9
+
+
+def test_restore_skips_a_damaged_newest_checkpoint(tmp_path, capsys):
+    m = CheckpointManager(str(tmp_path), keep=5, save_secs=None)
+    for step in (10, 20, 30):
+        m.save({"tensors": {"params": torch.full((4,), float(step))}, "meta": {"arch": "x"}}, step)
+    newest = m.latest()
+    with open(newest, "r+b") as f:                      # truncate the newest file in place (bit rot / short write on NFS)
+        f.truncate(16)
+    got = CheckpointManager(str(tmp_path)).restore()
+    assert got["meta"]["step"] == 20 and torch.equal(got["tensors"]["params"], torch.full((4,), 20.0))
+    assert "checkpoint_unreadable" in capsys.readouterr().out
+    for _, p in m.list():
+        with open(p, "r+b") as f:
+            f.truncate(8)
+    with pytest.raises(RuntimeError, match="no readable checkpoint"):
+        CheckpointManager(str(tmp_path)).restore()
