@@ -108,6 +108,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--cpu", action="store_true", help="force the CPU/gloo backend in every rank")
     p.add_argument("--log-dir", default=None, help="also write each rank's output to <dir>/rank-<r>.log")
     p.add_argument("--timeline", default=None, help="sets B200DP_TIMELINE for every rank")
+    p.add_argument("--check-build", "-cb", dest="check_build", action="store_true",
+                   help="print what this installation was built with (horovodrun --check-build) and exit")
     p.add_argument("command", nargs=argparse.REMAINDER)
     return p
 
@@ -294,11 +296,36 @@ def launch_once(args, slots: List[Slot], restart_count: int) -> int:
     return exit_code
 
 
+def check_build_report() -> str:
+    """What ``horovodrun --check-build`` prints, for this framework: data planes, kernels library, devices."""
+    import torch
+    from ..ops import _lib
+    from ..runtime import world as _w
+    box = lambda b: "[X]" if b else "[ ]"
+    lib_ok = _lib.available()
+    lines = ["b200dp build:", "", "Available frameworks:", f"    {box(True)} PyTorch {torch.__version__}",
+             f"    {box(False)} TensorFlow (the reference scripts' names are provided by `import b200dp as hvd`)", "",
+             "Available controllers:", f"    {box(False)} MPI (b200run accepts mpirun's argv)", f"    {box(_w.gloo_built())} Gloo", "",
+             "Available tensor operations:",
+             f"    {box(lib_ok)} NVLink peer-memory kernels (libb200dp.so, sm_100a){'' if lib_ok else ' - run tools/build.py'}",
+             f"    {box(False)} NCCL (baseline harness only)", f"    {box(_w.gloo_built())} Gloo (CPU tensors, control plane)", "",
+             f"library: {_lib.lib_path()}"]
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    lines.append(f"CUDA devices visible: {n}")
+    for d in range(n):
+        p = torch.cuda.get_device_properties(d)
+        lines.append(f"    {d}: {p.name}, sm_{p.major}{p.minor}, {p.multi_processor_count} SMs, {p.total_memory / 2**30:.0f} GiB")
+    return "\n".join(lines) + "\n"
+
+
 def main(argv: Optional[Sequence[str]] = None) -> int:
     args = build_parser().parse_args(list(argv) if argv is not None else None)
     cmd = list(args.command)
     if cmd and cmd[0] == "--":
         cmd = cmd[1:]
+    if args.check_build:
+        sys.stdout.write(check_build_report())
+        return 0
     if not cmd:
         sys.stderr.write("b200run: no command given\n")
         return 2

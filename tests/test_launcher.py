@@ -76,3 +76,9 @@ def test_max_restarts_reruns_job(tmp_path):
 def test_no_command_is_an_error():
     r = subprocess.run(RUN + ["-np", "1"], capture_output=True, text=True)
     assert r.returncode == 2
+
+
+def test_check_build_reports_data_planes():
+    r = subprocess.run(RUN + ["--check-build"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert "[X] Gloo" in r.stdout and "libb200dp.so" in r.stdout and "PyTorch" in r.stdout
