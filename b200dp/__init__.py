@@ -21,7 +21,7 @@ from .train.session import (MonitoredTrainingSession, SessionRunHook, BroadcastG
                             StopAtStepHook, LoggingTensorHook, StepCounterHook, CheckpointSaverHook, MetricsHook)
 from .train.trainer import Model, MNISTModel, SparseCategoricalCrossentropy
 from .train.engine import make_engine, TorchEngine, StepResult
-from .models.spec import get_spec
+from .models.spec import get_spec, ModelSpec, LayerSpec, custom as custom_spec
 from . import callbacks
 from . import elastic
 

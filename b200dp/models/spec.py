@@ -96,7 +96,7 @@ def _ch(base: int, width: float) -> int:
     return max(1, int(round(base * width)))
 
 
-def _build(arch: str, width: float, layers: List[LayerSpec]) -> ModelSpec:
+def _build(arch: str, width: float, layers: List[LayerSpec], num_classes: int = 10) -> ModelSpec:
     params: List[ParamSpec] = []
     off = 0
     h, w = 28, 28
@@ -131,7 +131,7 @@ def _build(arch: str, width: float, layers: List[LayerSpec]) -> ModelSpec:
             add(f"{nm}.kernel", (feat, u), "glorot_uniform", feat, u)
             add(f"{nm}.bias", (u,), "zeros")
             feat = u
-    return ModelSpec(arch=arch, width=width, layers=tuple(layers), params=tuple(params), total=off)
+    return ModelSpec(arch=arch, width=width, layers=tuple(layers), params=tuple(params), total=off, num_classes=num_classes)
 
 
 def mnist_cnn(width: float = 1.0) -> ModelSpec:
@@ -160,6 +160,37 @@ def keras128(width: float = 1.0) -> ModelSpec:
         LayerSpec("dropout", dict(rate=0.5)),
         LayerSpec("dense", dict(units=10, relu=False, name="out")),
     ])
+
+
+def custom(name: str, layers: List[LayerSpec], width: float = 1.0) -> ModelSpec:
+    """A user-defined 28x28 CNN from a layer list (``conv`` k/cout/padding/relu, ``pool``, ``flatten``, ``dense``
+    units/relu/name, ``dropout`` rate).  It gets the same flat parameter arena, checkpoints, collectives and training
+    loops as the built-in families; only ``mnist_cnn`` and ``keras128`` have hand-written sm_100a kernels, so a custom
+    spec trains through :class:`b200dp.train.engine.TorchEngine` (on the GPU when one is present)."""
+    if name in ARCHS:
+        raise ValueError(f"{name!r} is a built-in architecture")
+    kinds = {"conv", "pool", "flatten", "dense", "dropout"}
+    seen_flat = False
+    for L in layers:
+        if L.kind not in kinds:
+            raise ValueError(f"unknown layer kind {L.kind!r}; choose from {sorted(kinds)}")
+        if L.kind == "flatten":
+            seen_flat = True
+        if L.kind == "dense" and not seen_flat:
+            raise ValueError("a dense layer needs a flatten layer before it")
+        if L.kind in ("conv", "pool") and seen_flat:
+            raise ValueError(f"{L.kind} after flatten")
+        if L.kind == "conv":
+            L.args.setdefault("padding", "SAME")
+            L.args.setdefault("relu", True)
+            if L.args["padding"] not in ("SAME", "VALID"):
+                raise ValueError("conv padding must be SAME or VALID")
+        if L.kind == "dense":
+            L.args.setdefault("relu", False)
+    dense = [L for L in layers if L.kind == "dense"]
+    if not dense:
+        raise ValueError("the model needs a final dense layer producing the class logits")
+    return _build(name, width, list(layers), num_classes=int(dense[-1].args["units"]))
 
 
 ARCHS = {"mnist_cnn": mnist_cnn, "keras128": keras128}

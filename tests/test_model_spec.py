@@ -83,3 +83,27 @@ def test_bucket_planner():
     assert bs[1].start == dk.offset and bs[1].numel >= dk.numel
     with pytest.raises(ValueError):
         plan_arena_buckets(sp, [["conv1.", "dense."], ["conv2.", "out."]])
+
+
+def test_custom_spec_trains_through_the_torch_engine_and_checks_its_layers():
+    import numpy as np
+    import b200dp as hvd
+    L = hvd.LayerSpec
+    spec = hvd.custom_spec("tiny3", [L("conv", dict(k=3, cout=4, padding="VALID")), L("pool"), L("conv", dict(k=3, cout=8)), L("pool"),
+                                     L("flatten"), L("dense", dict(units=16, relu=True, name="fc")), L("dropout", dict(rate=0.1)),
+                                     L("dense", dict(units=3, name="out"))])
+    assert spec.num_classes == 3 and spec.param("fc.kernel").shape == (7 * 7 * 8, 16)      # 28 -> 26 -> 13 -> 13 -> 7
+    rng = np.random.RandomState(0)
+    x, y = rng.rand(48, 784).astype(np.float32), rng.randint(0, 3, 48)
+    x[np.arange(48), y * 200] = 5.0                          # an easy signal
+    m = hvd.Model(spec, seed=1)
+    m.compile(optimizer=hvd.Adam(5e-3), loss=hvd.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"])
+    h = m.fit(x, y, batch_size=16, epochs=6, verbose=0)
+    assert type(m.engine).__name__ == "TorchEngine" and h.history["loss"][-1] < h.history["loss"][0]
+    assert m.predict(x[:5]).shape == (5, 3)
+    for bad in ([L("dense", dict(units=3))], [L("flatten"), L("conv", dict(k=3, cout=2)), L("dense", dict(units=3))],
+                [L("conv", dict(k=3, cout=2)), L("flatten")], [L("attention"), L("flatten"), L("dense", dict(units=3))]):
+        with pytest.raises(ValueError):
+            hvd.custom_spec("bad", bad)
+    with pytest.raises(ValueError):
+        hvd.custom_spec("mnist_cnn", [L("flatten"), L("dense", dict(units=10))])
