@@ -73,6 +73,18 @@ class Engine:
                 "world_size": _w.size() if _w.is_initialized() else 1}
 
 
+class _NoSpan:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def _no_span(*_a, **_k):
+    return _NoSpan()
+
+
 class TorchEngine(Engine):
     """fp32 PyTorch engine (CPU by default).  Gradients come out of autograd
     already flat (the parameters are views of one leaf), get reduced in the
@@ -92,6 +104,7 @@ class TorchEngine(Engine):
         self.global_step = 0
         self.set_optimizer(optimizer)
         self._bucket_bytes = bucket_bytes
+        self.host_timeline = None            # a utils.timeline.HostTimeline when B200DP_TIMELINE / HOROVOD_TIMELINE is set
 
     def set_optimizer(self, optimizer) -> None:
         self.dist = _as_dist_adam(optimizer)
@@ -118,19 +131,23 @@ class TorchEngine(Engine):
             raise RuntimeError("no optimizer set; pass optimizer=Adam(...) or compile() the model")
         xt, yt = self._to_dev(x, y)
         self.params.grad = None
-        logits = self._forward(xt, training=True)
-        loss, correct = torch_ref.loss_and_metrics(logits, yt)
-        loss.backward()
+        span = self.host_timeline.span if self.host_timeline is not None else _no_span
+        with span("forward", "compute"):
+            logits = self._forward(xt, training=True)
+            loss, correct = torch_ref.loss_and_metrics(logits, yt)
+        with span("backward", "compute"):
+            loss.backward()
         g = self.params.grad
         if self.dist is not None and _w.is_initialized() and _w.size() > 1:
-            segs = [n for _, n in self.spec.segments()]
             if self.dist.op is C.Adasum:
                 # per-tensor Adasum over the fused buffer
-                for off, n in self.spec.segments():
-                    C.allreduce_(g[off:off + n], C.Adasum)
+                for p in self.spec.params:
+                    with span(f"adasum[{p.name}]", "collective"):
+                        C.allreduce_(g[p.offset:p.offset + p.numel], C.Adasum)
             else:
-                C.allreduce_(g, self.dist.op)
-        with torch.no_grad():
+                with span(f"allreduce[fused {g.numel() * 4} B]", "collective"):
+                    C.allreduce_(g, self.dist.op)
+        with torch.no_grad(), span("adam", "compute"):
             a = self.adam
             torch_ref.adam_step_(self.params.data, g, self.m, self.v, self.global_step + 1,
                                  lr=a.lr, beta1=a.beta1, beta2=a.beta2, eps=a.epsilon, eps_mode=a.eps_mode)

@@ -205,6 +205,11 @@ class MonitoredTrainingSession:
             self.engine.use_graph = False
             self._timeline = (Timeline(), tl_path)
             self._timeline[0].__enter__()
+        elif tl_path and hasattr(self.engine, "host_timeline"):
+            # CPU/gloo engine: host-side spans (forward, backward, every collective, the optimizer)
+            from ..utils.timeline import HostTimeline
+            self.engine.host_timeline = HostTimeline(_w.rank() if _w.is_initialized() else 0)
+            self._timeline = (self.engine.host_timeline, tl_path)
         self._entered = True
         return self
 
@@ -212,7 +217,10 @@ class MonitoredTrainingSession:
         if self._timeline is not None:
             tl, path = self._timeline
             self._timeline = None
-            tl.__exit__(None, None, None)
+            if hasattr(tl, "__exit__"):
+                tl.__exit__(None, None, None)
+            else:
+                self.engine.host_timeline = None
             r = _w.rank() if _w.is_initialized() else 0
             out = path if path.endswith(".json") and r == 0 else f"{path}.rank{r}.json"
             try:

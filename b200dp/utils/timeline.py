@@ -19,7 +19,8 @@ from ..ops import kernels as K
 
 _WRAPPED = ["conv1_pool_fwd", "conv1_wgrad", "head_fwd_bwd", "head_wgrad", "unpool_relu_bwd", "maxpool_fwd", "conv_direct_fwd",
             "conv_direct_dgrad", "conv_direct_wgrad", "gemm_simple", "cast_f32_to_bf16", "bias_relu_bf16", "adam_local",
-            "gemm_tc", "conv_tc_fwd", "conv_tc_dgrad", "conv_tc_wgrad"]
+            "gemm_tc", "gemm_tc_reduce_scatter", "conv_tc_fwd", "conv_tc_dgrad", "conv_tc_wgrad", "conv1_valid_fwd",
+            "conv1_valid_wgrad", "dropout_bf16"]
 
 
 class Timeline:
@@ -87,5 +88,44 @@ class Timeline:
         for ev in self.events():
             tid = streams.setdefault(ev["stream"], len(streams))
             tr.append({"name": ev["name"], "ph": "X", "ts": ev["start_us"], "dur": ev["dur_us"], "pid": 0, "tid": tid, "cat": "kernel"})
+        with open(path, "w") as f:
+            json.dump({"traceEvents": tr, "displayTimeUnit": "ns"}, f)
+
+
+class HostTimeline:
+    """Host-side spans (``time.perf_counter``) for the CPU/gloo engine: forward, backward, each gradient allreduce, the
+    optimizer.  This is what Horovod's timeline shows per tensor (NEGOTIATE / ALLREDUCE phases); there is no negotiation
+    here, so a collective is one span.  Same Chrome-trace output as :class:`Timeline`; ``pid`` is the rank."""
+
+    def __init__(self, rank: int = 0):
+        import time
+        self._now = time.perf_counter
+        self._t0 = self._now()
+        self.rank = rank
+        self.records: List[Tuple[str, str, float, float]] = []
+
+    def span(self, name: str, cat: str = "host"):
+        tl = self
+
+        class _Span:
+            def __enter__(self_inner):
+                self_inner.t = tl._now()
+                return self_inner
+
+            def __exit__(self_inner, *exc):
+                tl.records.append((name, cat, (self_inner.t - tl._t0) * 1e6, (tl._now() - self_inner.t) * 1e6))
+                return False
+        return _Span()
+
+    def summary(self) -> Dict[str, Dict[str, float]]:
+        agg = defaultdict(list)
+        for name, _, _, dur in self.records:
+            agg[name].append(dur)
+        return {k: {"calls": len(v), "mean_us": sum(v) / len(v), "min_us": min(v), "total_us": sum(v)} for k, v in agg.items()}
+
+    def save_chrome_trace(self, path: str) -> None:
+        cats: Dict[str, int] = {}
+        tr = [{"name": n, "ph": "X", "ts": ts, "dur": dur, "pid": self.rank, "tid": cats.setdefault(c, len(cats)), "cat": c}
+              for n, c, ts, dur in self.records]
         with open(path, "w") as f:
             json.dump({"traceEvents": tr, "displayTimeUnit": "ns"}, f)

@@ -121,3 +121,24 @@ def test_best_only_skips_worse_epochs(tmp_path):
     for e, v in enumerate([1.0, 0.5, 0.7, 0.4]):
         cb.on_epoch_end(e, {"val_loss": v})
     assert [os.path.basename(p) for p in cb.saved] == ["m-1.safetensors", "m-2.safetensors", "m-4.safetensors"]
+
+
+def test_timeline_env_writes_host_spans_for_the_cpu_engine(tmp_path, monkeypatch):
+    """HOROVOD_TIMELINE on the CPU/gloo engine: a Chrome trace with forward / backward / adam spans per step."""
+    import json
+    import numpy as np
+    import b200dp as hvd
+    out = tmp_path / "tl.json"
+    monkeypatch.setenv("HOROVOD_TIMELINE", str(out))
+    eng = hvd.make_engine(hvd.get_spec("mnist_cnn", 0.25), hvd.Adam(1e-3), engine="torch")
+    x, y = np.random.rand(8, 784).astype(np.float32), np.arange(8) % 10
+    with hvd.MonitoredTrainingSession(eng, hooks=[hvd.StopAtStepHook(last_step=3)]) as sess:
+        while not sess.should_stop():
+            sess.run(x, y)
+    assert eng.host_timeline is None                                   # detached at exit
+    tr = json.load(open(out))["traceEvents"]
+    names = [e["name"] for e in tr]
+    assert names.count("forward") == 3 and names.count("backward") == 3 and names.count("adam") == 3
+    assert all(e["ph"] == "X" and e["dur"] > 0 for e in tr)
+    fw = [e for e in tr if e["name"] == "forward"]
+    assert fw[0]["ts"] < fw[1]["ts"] < fw[2]["ts"]
