@@ -148,3 +148,12 @@ def test_elastic_state_single_process_commit_restore(tmp_path):
         assert ei.value.code == 75
     finally:
         del os.environ["B200DP_RESIZE_FILE"]
+
+
+@pytest.mark.parametrize("extra_args", [[], ["--fp16-allreduce", "--batches-per-allreduce", "2"], ["--use-adasum"]])
+def test_pytorch_example_keeps_replicas_identical(tmp_path, extra_args):
+    """Horovod's PyTorch recipe (any nn.Module + torch.optim) over the generic DistributedOptimizer, 2 ranks on gloo."""
+    r = _launch(2, [os.path.join(ROOT, "examples", "pytorch_mnist.py"), "--synthetic", "--train-samples", "512", "--test-samples", "128",
+                    "--batch-size", "32", "--epochs", "1", *extra_args])
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "replicas identical: True" in r.stdout and "Test set: Average loss:" in r.stdout
