@@ -4,8 +4,9 @@ The reference's sub-README points at an *external* elastic MPIJob manifest (``ho
 scripts recover through rank-0 checkpoints (``horovod/tensorflow_mnist.py:157-167``).  This module gives the Horovod
 elastic programming model — a state object with ``commit`` / ``restore`` / ``sync`` and a ``run`` decorator — on top of
 what this framework actually does when a rank dies: the launcher tears the job down at once and, with
-``b200run --max-restarts N``, starts it again (possibly with a different ``-np``), and the new incarnation picks up
-from the last commit.  World membership therefore changes *between* incarnations, never inside a running process:
+``b200run --max-restarts N``, starts it again, and the new incarnation picks up from the last commit.  A resize works the
+same way (``b200run --resize-file PATH``: the file holds the new rank count; the next commit exits with code 75 and the
+launcher relaunches with that many ranks).  World membership therefore changes *between* incarnations, never inside a running process:
 peer-mapped NVLink segments cannot lose a peer and keep going.
 
     state = hvd.elastic.EngineState(engine, epoch=0, batch=0)

@@ -105,6 +105,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--master-port", type=int, default=None)
     p.add_argument("--max-restarts", type=int, default=0)
     p.add_argument("--grace-secs", type=float, default=5.0)
+    p.add_argument("--resize-file", default=None,
+                   help="elastic resize: ranks see this path as B200DP_RESIZE_FILE; when it exists (content: the new -np) the next "
+                        "hvd.elastic commit exits with code 75 and the job is relaunched with that many ranks")
     p.add_argument("--cpu", action="store_true", help="force the CPU/gloo backend in every rank")
     p.add_argument("--log-dir", default=None, help="also write each rank's output to <dir>/rank-<r>.log")
     p.add_argument("--timeline", default=None, help="sets B200DP_TIMELINE for every rank")
@@ -208,6 +211,8 @@ def launch_once(args, slots: List[Slot], restart_count: int) -> int:
             env_rank["B200DP_FORCE_CPU"] = "1"
         if args.timeline:
             env_rank["B200DP_TIMELINE"] = args.timeline
+        if args.resize_file:
+            env_rank["B200DP_RESIZE_FILE"] = os.path.abspath(args.resize_file)
         if _is_local(s.host):
             env = dict(base_env)
             env.update(exports)
@@ -342,10 +347,31 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
         return 2
     slots = map_by_slot(hosts, np_)
     restarts = 0
+    incarnation = 0
     while True:
-        rc = launch_once(args, slots, restarts)
+        rc = launch_once(args, slots, incarnation)
+        if rc == 75 and args.resize_file and os.path.exists(args.resize_file):
+            # elastic resize requested at a commit point: relaunch with the new world size (not a failure: no restart is spent)
+            try:
+                new_np = int(open(args.resize_file).read().strip() or np_)
+            except ValueError:
+                new_np = np_
+            os.remove(args.resize_file)
+            if not args.hostfile and not args.hosts:
+                hosts = [("localhost", new_np)]
+            try:
+                slots = map_by_slot(hosts, new_np)
+            except Exception as e:
+                sys.stderr.write(f"b200run: cannot resize to {new_np} ranks: {e}\n")
+                return 2
+            sys.stderr.write(f"b200run: resizing {np_} -> {new_np} ranks at the last commit\n")
+            sys.stderr.flush()
+            np_ = new_np
+            incarnation += 1
+            continue
         if rc == 0 or restarts >= args.max_restarts or rc >= 128:
             return rc
+        incarnation += 1
         restarts += 1
         sys.stderr.write(f"b200run: job failed with code {rc}; restart {restarts}/{args.max_restarts} from the latest checkpoint\n")
         sys.stderr.flush()

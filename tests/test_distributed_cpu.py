@@ -157,3 +157,19 @@ def test_pytorch_example_keeps_replicas_identical(tmp_path, extra_args):
                     "--batch-size", "32", "--epochs", "1", *extra_args])
     assert r.returncode == 0, r.stderr[-3000:]
     assert "replicas identical: True" in r.stdout and "Test set: Average loss:" in r.stdout
+
+
+def test_elastic_resize_relaunches_with_the_new_world_size(tmp_path):
+    """A resize request (file naming the new -np) is honoured at the next commit: every rank exits 75, b200run relaunches
+    with 4 ranks, the new incarnation syncs the last commit from rank 0 and finishes."""
+    flag = tmp_path / "resize"
+    flag.write_text("4\n")
+    r = _launch(2, [os.path.join(W, "elastic_worker.py"), str(tmp_path), "-1", "0"], extra=["--resize-file", str(flag), "--grace-secs", "2"])
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "resizing 2 -> 4 ranks" in r.stderr and not flag.exists()
+    res = [json.load(open(p)) for p in sorted(glob.glob(str(tmp_path / "r*.json")))]
+    assert len(res) == 4
+    for d in res:
+        assert d["restart"] == 1 and d["first_batch"] == 4 and d["final_batch"] == 12 and d["global_step"] == 12
+        assert d["resets"] == [1] and d["commits"] == 3
+    assert len({d["digest"] for d in res}) == 1
