@@ -107,3 +107,30 @@ def test_custom_spec_trains_through_the_torch_engine_and_checks_its_layers():
             hvd.custom_spec("bad", bad)
     with pytest.raises(ValueError):
         hvd.custom_spec("mnist_cnn", [L("flatten"), L("dense", dict(units=10))])
+
+
+from hypothesis import given, settings, strategies as st
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.lists(st.integers(min_value=0, max_value=1 << 22), max_size=40), st.integers(min_value=1, max_value=1 << 22))
+def test_plan_buckets_invariants(sizes, cap):
+    """Every tensor lands in exactly one bucket, ready order is kept, a bucket only exceeds the cap when it is one tensor."""
+    bs = plan_buckets(sizes, cap)
+    assert [i for b in bs for i in b] == list(range(len(sizes)))
+    for b in bs:
+        assert b and (sum(sizes[i] for i in b) <= cap or len(b) == 1)
+    for a, b in zip(bs, bs[1:]):                      # greedy: the next tensor really did not fit
+        assert sum(sizes[i] for i in a) + sizes[b[0]] > cap
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.sampled_from(["mnist_cnn", "keras128"]), st.sampled_from([0.25, 0.5, 1.0, 1.5, 2.0, 6.0]))
+def test_arena_buckets_tile_every_width(arch, width):
+    sp = S.get_spec(arch, width)
+    bs = plan_arena_buckets(sp, [["dense.bias", "out."], ["dense.kernel"], ["conv1.", "conv2."]])
+    assert sorted((b.start, b.end) for b in bs)[0][0] == 0 and sum(b.numel for b in bs) == sp.total
+    for b in bs:
+        assert b.start % S.ALIGN_ELEMS == 0                   # 256-byte aligned ranges: vectorised kernels need no peeling
+        assert all(b.start <= o and o + n <= b.end for o, n in b.segments)
+    assert sum(n for b in bs for _, n in b.segments) == sp.num_params
