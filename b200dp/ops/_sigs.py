@@ -62,6 +62,11 @@ _SIGS = {
     "b200_conv_tc_fwd_pad": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "b200_conv_tc_dgrad_pad": (I, [P, P, P, I, I, I, I, I, I, I, P]),
     "b200_conv_tc_wgrad_pad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "b200_loader_create": (I, [P, P, LL, SZ, I, I, I, U64, C.POINTER(P), C.POINTER(P), C.POINTER(P)]),
+    "b200_loader_next": (I, [P, PI, PLL]),
+    "b200_loader_release": (I, [P, I]),
+    "b200_loader_batches_per_epoch": (LL, [P]),
+    "b200_loader_destroy": (I, [P]),
     "b200_topology_json": (I, [C.c_char_p, I]),
     "b200_l2_flush": (I, [P, SZ, P]),
     "b200_stream_l2_persist": (I, [P, SZ, F, P]),

@@ -243,6 +243,15 @@ class Model:
         log = get_logger()
         order = rng.permutation(n) if shuffle else np.arange(n)
         cursor = 0
+        # batches are assembled by the native loader thread (csrc/loader.cpp) while the previous step is being issued;
+        # B200DP_NATIVE_LOADER=0 keeps the gather in this loop
+        loader = None
+        if os.environ.get("B200DP_NATIVE_LOADER", "1") != "0" and batch_size <= n and x.dtype == np.float32:
+            try:
+                from ..data.loader import BatchLoader
+                loader = BatchLoader(x, y, batch_size, shuffle=shuffle, seed=int(rng.randint(0, 2 ** 31 - 1)))
+            except (RuntimeError, OSError, ValueError):
+                loader = None
         self.stop_training = False
         for epoch in range(initial_epoch, epochs):
             for cb in cbs:
@@ -253,12 +262,17 @@ class Model:
             seen = 0
             pending: List[StepResult] = []
             for b in range(steps_per_epoch):
-                if cursor + batch_size > n:
-                    order = rng.permutation(n) if shuffle else np.arange(n)
-                    cursor = 0
-                idx = order[cursor:cursor + batch_size]
-                cursor += batch_size
-                res = self.engine.train_step(x[idx], y[idx])
+                if loader is not None:
+                    xb, yb = loader.next()
+                    # numpy views: the engine copies them into its own staging before returning, so the slot is free again
+                    res = self.engine.train_step(xb.numpy(), yb.numpy())
+                else:
+                    if cursor + batch_size > n:
+                        order = rng.permutation(n) if shuffle else np.arange(n)
+                        cursor = 0
+                    idx = order[cursor:cursor + batch_size]
+                    cursor += batch_size
+                    res = self.engine.train_step(x[idx], y[idx])
                 pending.append(res)
                 if len(pending) >= 64 or b == steps_per_epoch - 1:
                     for r in pending:       # one sync for many steps
@@ -293,6 +307,8 @@ class Model:
                          images_per_sec=round(steps_per_epoch * batch_size * ws / max(dt, 1e-9), 1), **logs)
             if self.stop_training:
                 break
+        if loader is not None:
+            loader.close()
         for cb in cbs:
             cb.on_train_end()
         return hist

@@ -175,6 +175,19 @@ int b200_conv_tc_dgrad_pad(const void* dout, const void* w, void* din, int B, in
 int b200_conv_tc_wgrad_pad(const void* in, const void* dout, float* dw, float* dbias, int B, int H, int W, int Ci,
                            int Co, int k, int pad, void* stream);
 
+/* ---- native minibatch loader (host threads; no CUDA calls) ----
+ * Infinite shuffled-minibatch stream with the reference generator's semantics (horovod/tensorflow_mnist.py:76-85): a fresh
+ * permutation per pass, consecutive full batches, tail dropped.  One producer thread copies rows into the caller's ring of
+ * slots (slot_x[i]: batch*row_bytes bytes, slot_y[i]: batch int32 labels; pinned memory on a GPU box).  Batches come out in
+ * order; a slot must be released before the producer may overwrite it. */
+typedef void* b200_loader_t;
+int b200_loader_create(const void* x, const int* y, long long n, size_t row_bytes, int batch, int nslots, int shuffle,
+                       uint64_t seed, void* const* slot_x, int* const* slot_y, b200_loader_t* out);
+int b200_loader_next(b200_loader_t loader, int* slot, long long* batch_index);
+int b200_loader_release(b200_loader_t loader, int slot);
+long long b200_loader_batches_per_epoch(b200_loader_t loader);
+int b200_loader_destroy(b200_loader_t loader);
+
 /* ---- host runtime ---- */
 /* JSON description of the visible GPUs: names, SM counts, memory, peer-access matrix. Returns bytes written. */
 int b200_topology_json(char* buf, int buflen);
