@@ -99,9 +99,24 @@ def preprocess(x: np.ndarray) -> np.ndarray:
 def train_input_generator(x_train: np.ndarray, y_train: np.ndarray, batch_size: int = 64,
                           seed: Optional[int] = None) -> Iterator[Tuple[np.ndarray, np.ndarray]]:
     """Infinite generator; fresh permutation every pass; tail dropped.  Unseeded by
-    default, so ranks draw different orders (the reference's behaviour)."""
+    default, so ranks draw different orders (the reference's behaviour).  With the native loader the yielded arrays
+    alias a ring slot and stay valid until four more batches have been drawn (copy them to keep them longer)."""
     assert len(x_train) == len(y_train)
     rng = np.random.RandomState(seed) if seed is not None else np.random
+    if os.environ.get("B200DP_NATIVE_LOADER", "1") != "0" and x_train.dtype == np.float32 and 1 <= batch_size <= len(x_train):
+        # same stream semantics, rows gathered by the native producer thread while the caller trains on the previous batch
+        try:
+            from .loader import BatchLoader
+            ld = BatchLoader(x_train, y_train, batch_size, seed=int(rng.randint(0, 2 ** 31 - 1)), nslots=8, hold=4)
+        except (RuntimeError, OSError, ValueError):
+            ld = None
+        if ld is not None and ld.native:
+            try:
+                while True:
+                    xb, yb = ld.next()
+                    yield xb.numpy(), yb.numpy()            # views of a ring slot: valid until four more batches were drawn
+            finally:
+                ld.close()
     while True:
         p = rng.permutation(len(x_train))
         x_train, y_train = x_train[p], y_train[p]
