@@ -228,6 +228,11 @@ class B200Engine(Engine):
         self._graphs.clear()
         self._plan_comm()
 
+    def set_lr(self, lr: float) -> None:
+        """The kernels read the learning rate from device memory at run time, so a new value needs no graph re-capture."""
+        super().set_lr(lr)
+        self.hyper_dev[0:1].fill_(float(lr))
+
     def _plan_comm(self) -> None:
         """Static bucket plan: which ranges each comm kernel reduces, and with which algorithm."""
         buckets = plan_arena_buckets(self.spec, [["dense.bias", "out."], ["dense.kernel"], ["conv1.", "conv2."]])

@@ -64,6 +64,15 @@ class Engine:
     def broadcast_state(self, root_rank: int = 0) -> None: ...
 
     # shared helpers ---------------------------------------------------------
+    def set_lr(self, lr: float) -> None:
+        """Change the learning rate without rebuilding anything (LR schedules / warm-up callbacks)."""
+        from dataclasses import replace
+        if getattr(self, "adam", None) is None:
+            raise RuntimeError("no optimizer set")
+        self.adam = replace(self.adam, lr=float(lr))
+        if getattr(self, "dist", None) is not None:
+            self.dist = replace(self.dist, base=self.adam)
+
     def weights(self) -> Dict[str, torch.Tensor]:
         flat = self.state()["tensors"]["params"]
         return {k: v.clone() for k, v in self.spec.views(flat).items()}

@@ -146,6 +146,66 @@ class History(Callback):
             self.history.setdefault(k, []).append(v)
 
 
+class LearningRateScheduleCallback(Callback):
+    """``hvd.callbacks.LearningRateScheduleCallback``: lr = initial_lr * multiplier for epochs in [start_epoch, end_epoch).
+    ``multiplier`` is a number or ``f(epoch)``; with ``staircase=False`` the epoch passed to ``f`` is fractional and the
+    rate is updated every batch."""
+
+    def __init__(self, initial_lr: float, multiplier, start_epoch: int = 0, end_epoch: Optional[int] = None,
+                 staircase: bool = True, steps_per_epoch: Optional[int] = None):
+        self.initial_lr = float(initial_lr)
+        self.multiplier = multiplier if callable(multiplier) else (lambda epoch: multiplier)
+        self.start_epoch, self.end_epoch, self.staircase = start_epoch, end_epoch, staircase
+        self.steps_per_epoch = steps_per_epoch
+        self._epoch = 0
+        self.history: List[float] = []
+
+    def _active(self, epoch: float) -> bool:
+        return epoch >= self.start_epoch and (self.end_epoch is None or epoch < self.end_epoch)
+
+    def _apply(self, epoch: float) -> None:
+        if self._active(epoch):
+            lr = self.initial_lr * float(self.multiplier(epoch))
+            self.model.engine.set_lr(lr)
+            self.history.append(lr)
+
+    def on_epoch_begin(self, epoch, logs=None):
+        self._epoch = epoch
+        self._apply(epoch)
+
+    def on_train_batch_end(self, batch, logs=None):
+        if not self.staircase:
+            spe = self.steps_per_epoch or getattr(self.model, "_steps_per_epoch", None)
+            if spe:
+                self._apply(self._epoch + (batch + 1) / spe)
+
+    def on_epoch_end(self, epoch, logs=None):
+        if logs is not None:
+            logs["lr"] = self.model.engine.adam.lr
+
+
+class LearningRateWarmupCallback(LearningRateScheduleCallback):
+    """``hvd.callbacks.LearningRateWarmupCallback``: ramp from ``initial_lr / size`` to ``initial_lr`` over the first
+    ``warmup_epochs`` epochs, batch by batch (Goyal et al.) — the companion of the lr x size rule the reference applies
+    (``horovod/tensorflow_mnist.py:123-130``)."""
+
+    def __init__(self, initial_lr: float, warmup_epochs: int = 5, steps_per_epoch: Optional[int] = None, verbose: int = 0):
+        size = _w.size() if _w.is_initialized() else 1
+
+        def mult(epoch):
+            return 1.0 / size * (epoch * (size - 1) / warmup_epochs + 1)
+        super().__init__(initial_lr, mult, start_epoch=0, end_epoch=warmup_epochs, staircase=False, steps_per_epoch=steps_per_epoch)
+        self.verbose = verbose
+        self.warmup_epochs = warmup_epochs
+
+    def on_epoch_end(self, epoch, logs=None):
+        super().on_epoch_end(epoch, logs)
+        if epoch == self.warmup_epochs - 1:
+            self.model.engine.set_lr(self.initial_lr)
+            if self.verbose:
+                get_logger().info("lr_warmup_done", epoch=epoch + 1, lr=self.initial_lr)
+
+
 class MetricsCallback(Callback):
     """Feeds the Prometheus exporter (:mod:`b200dp.utils.metrics`) every ``every_n_batches`` batches and at epoch end."""
 
@@ -235,6 +295,7 @@ class Model:
         if exp is not None and not any(isinstance(c, MetricsCallback) for c in cbs):
             cbs.append(MetricsCallback(exp))
         self._last_batch = batch_size
+        self._steps_per_epoch = steps_per_epoch
         for cb in cbs:
             cb.set_model(self)
         for cb in cbs:

@@ -142,3 +142,43 @@ def test_timeline_env_writes_host_spans_for_the_cpu_engine(tmp_path, monkeypatch
     assert all(e["ph"] == "X" and e["dur"] > 0 for e in tr)
     fw = [e for e in tr if e["name"] == "forward"]
     assert fw[0]["ts"] < fw[1]["ts"] < fw[2]["ts"]
+
+
+def test_lr_schedule_and_warmup_callbacks(monkeypatch):
+    import numpy as np
+    import b200dp as hvd
+    from b200dp.data import mnist
+    from b200dp.train import trainer as T
+    (x, y), _ = mnist.synthetic_mnist(64, 8, seed=2)
+    x = mnist.preprocess(x)
+
+    def model():
+        m = hvd.Model(hvd.get_spec("mnist_cnn", 0.25), engine="torch", seed=1)
+        m.compile(optimizer=hvd.Adam(1e-3), loss=hvd.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"])
+        return m
+    # staircase schedule: x1 for epoch 0, x0 afterwards -> the weights stop moving after the first epoch
+    m = model()
+    sched = hvd.callbacks.LearningRateScheduleCallback(1e-3, lambda e: 1.0 if e < 1 else 0.0)
+    snaps = []
+
+    class Snap(hvd.callbacks.Callback):
+        def on_epoch_end(self, epoch, logs=None):
+            snaps.append(self.model.engine.params.data.clone())
+    h = m.fit(x, y, batch_size=16, epochs=3, verbose=0, callbacks=[sched, Snap()])
+    assert sched.history == [1e-3, 0.0, 0.0] and h.history["lr"] == [1e-3, 0.0, 0.0]
+    assert torch_equal(snaps[1], snaps[2]) and not torch_equal(snaps[0], m.engine.params.data * 0)
+    # warm-up in a world of 4: starts at lr/4, climbs every batch, lands on lr exactly
+    monkeypatch.setattr(T._w, "is_initialized", lambda: True)
+    monkeypatch.setattr(T._w, "size", lambda: 4)
+    warm = hvd.callbacks.LearningRateWarmupCallback(4e-3, warmup_epochs=2)
+    monkeypatch.undo()
+    m2 = model()
+    m2.fit(x, y, batch_size=16, epochs=3, verbose=0, callbacks=[warm])
+    hs = warm.history
+    assert abs(hs[0] - 1e-3) < 1e-12 and all(b >= a for a, b in zip(hs, hs[1:])) and max(hs) <= 4e-3 + 1e-12
+    assert m2.engine.adam.lr == 4e-3 and m2.engine.state()["meta"]["optimizer"]["lr"] == 4e-3
+
+
+def torch_equal(a, b):
+    import torch
+    return bool(torch.equal(a, b))
