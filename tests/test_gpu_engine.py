@@ -157,3 +157,25 @@ def test_keras128_through_model_api(data):
     hist = m.fit(x, y, batch_size=64, epochs=2, verbose=0)
     assert type(m.engine).__name__ == "B200Engine" and m.engine.keras
     assert hist.history["loss"][-1] < hist.history["loss"][0]
+
+
+def test_set_lr_takes_effect_without_graph_recapture(data):
+    """LR schedules: the kernels read the rate from device memory, so set_lr() needs no new CUDA graph."""
+    x, y, _, _ = data
+    B = 64
+    g, _ = _pair(B, True, use_graph=True)
+    for s in range(4):
+        g.train_step(x[s * B:(s + 1) * B], y[s * B:(s + 1) * B])
+    graphs = dict(g._graphs)
+    assert len(graphs) == 2
+    g.set_lr(0.0)
+    torch.cuda.synchronize()
+    before = g.master.clone()
+    for s in range(2):
+        g.train_step(x[s * B:(s + 1) * B], y[s * B:(s + 1) * B])
+    torch.cuda.synchronize()
+    assert torch.equal(g.master, before)                       # zero rate: Adam's update is exactly zero
+    g.set_lr(1e-3)
+    g.train_step(x[:B], y[:B])
+    torch.cuda.synchronize()
+    assert not torch.equal(g.master, before) and g._graphs == graphs and g.state()["meta"]["optimizer"]["lr"] == 1e-3
