@@ -307,6 +307,9 @@ int b200_conv_res_launch(int mode, const void* act, const void* w, const void* b
   const size_t fixed = 1024 + (size_t)ntaps * p.wtile_bytes + (ntaps + 6 + 2 * NACC) * 8 + 64 + (size_t)N * 4;
   const int grid = B < 148 ? B : 148;
   p.nbuf = (B > grid && fixed + 2 * (size_t)p.img_bytes <= 220 * 1024) ? 2 : 1;   // a second buffer only pays with >1 image per CTA
+  // Several images per CTA through ONE buffer (image too large to double-buffer, e.g. the keras128 dgrad at batch > 148)
+  // serialises load and MMA and has not been measured against the shifted-TMA kernel: leave those launches to it.
+  if (p.nbuf == 1 && B > grid) return B200_ERR_UNSUPPORTED;
   const size_t smem = fixed + (size_t)p.nbuf * p.img_bytes;
   if (smem > 220 * 1024) return B200_ERR_UNSUPPORTED;
 
