@@ -109,7 +109,9 @@ def build_parser() -> argparse.ArgumentParser:
                    help="elastic resize: ranks see this path as B200DP_RESIZE_FILE; when it exists (content: the new -np) the next "
                         "hvd.elastic commit exits with code 75 and the job is relaunched with that many ranks")
     p.add_argument("--cpu", action="store_true", help="force the CPU/gloo backend in every rank")
-    p.add_argument("--log-dir", default=None, help="also write each rank's output to <dir>/rank-<r>.log")
+    p.add_argument("--log-dir", "--output-filename", "-output-filename", dest="log_dir", default=None,
+                   help="also write each rank's output to <dir>/rank-<r>.log (mpirun: --output-filename)")
+    p.add_argument("-wdir", "--wdir", "-wd", dest="wdir", default=None, help="working directory of every rank (mpirun: -wdir)")
     p.add_argument("--timeline", default=None, help="sets B200DP_TIMELINE for every rank")
     p.add_argument("--check-build", "-cb", dest="check_build", action="store_true",
                    help="print what this installation was built with (horovodrun --check-build) and exit")
@@ -228,10 +230,10 @@ def launch_once(args, slots: List[Slot], restart_count: int) -> int:
                     except OSError:
                         pass
             p = subprocess.Popen(args.command, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
-                                 preexec_fn=_pre)
+                                 preexec_fn=_pre, cwd=args.wdir or None)
         else:
             envs = " ".join(f"{k}={shlex.quote(v)}" for k, v in {**exports, **env_rank}.items())
-            remote = f"cd {shlex.quote(os.getcwd())} && env {envs} {' '.join(shlex.quote(c) for c in args.command)}"
+            remote = f"cd {shlex.quote(args.wdir or os.getcwd())} && env {envs} {' '.join(shlex.quote(c) for c in args.command)}"
             p = subprocess.Popen(["ssh", "-o", "StrictHostKeyChecking=no", "-o", "UserKnownHostsFile=/dev/null",
                                   s.host, remote], stdout=subprocess.PIPE, stderr=subprocess.PIPE,
                                  preexec_fn=os.setsid)

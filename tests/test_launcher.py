@@ -82,3 +82,16 @@ def test_check_build_reports_data_planes():
     r = subprocess.run(RUN + ["--check-build"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr
     assert "[X] Gloo" in r.stdout and "libb200dp.so" in r.stdout and "PyTorch" in r.stdout
+
+
+def test_mpirun_wdir_and_output_filename(tmp_path):
+    wd = tmp_path / "wd"
+    wd.mkdir()
+    logs = tmp_path / "logs"
+    r = _run(["-np", "2", "-wdir", str(wd), "--output-filename", str(logs)], """
+        import os
+        print("cwd", os.getcwd(), os.environ["RANK"])
+    """, timeout=60)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.count(f"cwd {wd}") == 2
+    assert sorted(os.listdir(logs)) == ["rank-0.log", "rank-1.log"] and f"cwd {wd} 1" in (logs / "rank-1.log").read_text()
