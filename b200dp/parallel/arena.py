@@ -298,6 +298,16 @@ class SymmetricArena:
         return cur
 
     def _adasum_(self, flat: torch.Tensor, seg_numel: List[int]) -> None:
+        lim = 32                                   # tensors per kernel call (B200_MAX_SEGMENTS)
+        if len(seg_numel) > lim:
+            # a bucket with more tensors than one call takes: reduce it in runs of `lim` tensors
+            off = 0
+            for i in range(0, len(seg_numel), lim):
+                part = seg_numel[i:i + lim]
+                m = sum(part)
+                self._adasum_(flat[off:off + m], part)
+                off += m
+            return
         n = flat.numel()
         self._ensure_staging(n)
         if n > self._staging_elems:
@@ -309,11 +319,6 @@ class SymmetricArena:
         for s in seg_numel:
             starts.append(off)
             off += s
-        # chunk the segment list to the kernel's per-call limit
-        res = ping
-        lim = 32
-        if len(seg_numel) > lim:
-            raise K.B200Error(f"at most {lim} tensors per fused Adasum call")
         res = self.adasum_levels(self._staging, ping, pong, scratch, starts, seg_numel)
         flat.copy_(self.view(self._staging, res, n, torch.float32))
 
