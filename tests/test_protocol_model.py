@@ -106,3 +106,79 @@ def test_the_checker_catches_broken_protocols(variant):
         except Violation:
             caught += 1
     assert caught > 0, f"mutant {variant} survived every schedule"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Two-shot bucket: owner-sharded Adam, updated bf16 weights PUSHED into every peer's working copy.
+#
+#   step t on rank r:
+#     forward/backward READ w16[r][*]  (all slices)           — must see version t everywhere
+#     barrier A(t)   (launched only after this rank's last read of those weights: the dense dgrad)
+#     owner work: reduce slice r, Adam -> version t+1, store w16[q][r] = t+1 into EVERY rank q (peer stores)
+#     barrier B(t)
+#   then step t+1 reads version t+1.
+# Hazards: a fast rank's push landing in a slow rank's working copy while that rank still reads version t (prevented by
+# A), and a rank starting step t+1 before every owner's push has landed (prevented by B).
+# ---------------------------------------------------------------------------------------------------------------------
+def twoshot_proc(r, n, steps, mem, variant):
+    def barrier(name, t):
+        for q in range(n):
+            mem[name][q][r] = t + 1
+            yield
+        while any(mem[name][r][q] < t + 1 for q in range(n)):
+            yield
+
+    for t in range(steps):
+        # forward + backward: read every slice of the local working copy, twice (fwd and dgrad), with yields in between
+        for _ in range(2):
+            for s in range(n):
+                if mem["w16"][r][s] != t:
+                    raise Violation(f"rank {r} step {t}: slice {s} of its working weights is version {mem['w16'][r][s]}")
+                yield
+        if variant != "push_before_A":
+            yield from barrier("A", t)
+        for q in range(n):                                   # owner r: push its updated slice to everyone
+            mem["w16"][q][r] = t + 1
+            yield
+        if variant == "push_before_A":
+            yield from barrier("A", t)
+        if variant != "no_B":
+            yield from barrier("B", t)
+        mem["reduced"][r] = t + 1
+
+
+def run_twoshot(n, steps, seed, variant="correct"):
+    rng = random.Random(seed)
+    mem = {"w16": [[0] * n for _ in range(n)], "A": [[0] * n for _ in range(n)], "B": [[0] * n for _ in range(n)], "reduced": [0] * n}
+    procs = {r: twoshot_proc(r, n, steps, mem, variant) for r in range(n)}
+    slow, ticks = rng.randrange(n), 0
+    while procs:
+        ticks += 1
+        if ticks % 41 == 0:
+            slow = rng.randrange(n)
+        r = rng.choice(list(procs))
+        if r == slow and len(procs) > 1 and rng.random() < 0.85:
+            continue
+        try:
+            next(procs[r])
+        except StopIteration:
+            del procs[r]
+        if ticks > 2_000_000:
+            raise RuntimeError("model deadlocked")
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_twoshot_weight_push_is_race_free_with_its_two_barriers(n):
+    for seed in range(200):
+        run_twoshot(n, steps=8, seed=seed)
+
+
+@pytest.mark.parametrize("variant", ["push_before_A", "no_B"])
+def test_twoshot_mutants_are_caught(variant):
+    caught = 0
+    for seed in range(200):
+        try:
+            run_twoshot(4, steps=6, seed=seed, variant=variant)
+        except Violation:
+            caught += 1
+    assert caught > 0, f"mutant {variant} survived every schedule"
