@@ -117,10 +117,11 @@ def train_input_generator(x_train: np.ndarray, y_train: np.ndarray, batch_size: 
                     yield xb.numpy(), yb.numpy()            # views of a ring slot: valid until four more batches were drawn
             finally:
                 ld.close()
+    # pure-Python twin of the native stream: one index permutation per pass and a cursor into it; the arrays themselves are
+    # never reordered, a batch is one fancy-index gather, and the rows that do not fill a last batch are skipped
+    n_full = len(x_train) // batch_size
     while True:
-        p = rng.permutation(len(x_train))
-        x_train, y_train = x_train[p], y_train[p]
-        index = 0
-        while index <= len(x_train) - batch_size:
-            yield x_train[index:index + batch_size], y_train[index:index + batch_size]
-            index += batch_size
+        order = rng.permutation(len(x_train))
+        for b in range(n_full):
+            rows = order[b * batch_size:(b + 1) * batch_size]
+            yield x_train[rows], y_train[rows]

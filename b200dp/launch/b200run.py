@@ -269,6 +269,7 @@ def launch_once(args, slots: List[Slot], restart_count: int) -> int:
         while alive:
             if stop["sig"] is not None:
                 exit_code = 128 + stop["sig"]
+                args._launcher_signalled = True      # the operator (or the pod) stopped the JOB: never restart after this
                 break
             for r in list(alive):
                 rc = procs[r].poll()
@@ -371,7 +372,9 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
             np_ = new_np
             incarnation += 1
             continue
-        if rc == 0 or restarts >= args.max_restarts or rc >= 128:
+        # A rank that died of a signal (OOM-killer SIGKILL -> 137, SIGSEGV -> 139, SIGABRT -> 134) is a failure like any
+        # other and is restarted from the latest checkpoint; only a signal delivered to the launcher itself ends the job.
+        if rc == 0 or restarts >= args.max_restarts or getattr(args, "_launcher_signalled", False):
             return rc
         incarnation += 1
         restarts += 1

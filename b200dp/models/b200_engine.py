@@ -93,6 +93,9 @@ class B200Engine(Engine):
         self.global_step = 0
         self.launches_per_step = 0
         self._nvtx = _env_flag("B200DP_NVTX", "0")      # NVTX ranges around the phases of a step (for nsys / ncu --nvtx)
+        self.sample_comm_timing = False                  # True: the next step runs eagerly with CUDA events around its collectives
+        self._comm_events: List[Tuple[torch.cuda.Event, torch.cuda.Event]] = []
+        self._timing_now = False
 
         L = self.spec.layers
         self.C1 = L[0].args["cout"]
@@ -174,9 +177,17 @@ class B200Engine(Engine):
         self.a1 = e(B, H1, H1, self.C1)
         self.am1 = None if self.keras else e(B, H1, H1, self.C1, dt=torch.uint8)
         self.c2 = None if self.tc_conv else e(B, H2, H2, self.C2)
-        self.a2, self.am2 = e(B, HP, HP, self.C2), e(B, HP, HP, self.C2, dt=torch.uint8)
+        # a2 (flattened conv features) and dz are what the peers gather for the fused dense wgrad: they live in a symmetric
+        # segment [a2 | dz | gathered a2 slices of all ranks | gathered dz of all ranks]
+        self.ACT_A2, self.ACT_DZ = 0, B * self.F * 2
+        self.ACT_A2G = self.ACT_DZ + B * self.D * 2
+        self.ACT_DZG = self.ACT_A2G + B * self.F * 2
+        self.seg_act = a.alloc(self.ACT_DZG + self.n * B * self.D * 2)
+        self.a2 = a.view(self.seg_act, self.ACT_A2, B * self.F, bf16).view(B, HP, HP, self.C2)
+        self.dz = a.view(self.seg_act, self.ACT_DZ, B * self.D, bf16).view(B, self.D)
+        self.am2 = e(B, HP, HP, self.C2, dt=torch.uint8)
         self.z = torch.zeros(B, self.D, device=dev)
-        self.h, self.dz = e(B, self.D), e(B, self.D)
+        self.h = e(B, self.D)
         self.dlogits, self.logits = e(B, self.NC, dt=torch.float32), e(B, self.NC, dt=torch.float32)
         self.dpool, self.dy2, self.da1 = e(B, HP, HP, self.C2), e(B, H2, H2, self.C2), e(B, H1, H1, self.C1)
         self._pinned = [(torch.empty(B, 784).pin_memory(), torch.empty(B, dtype=torch.int32).pin_memory(), torch.cuda.Event())
@@ -184,6 +195,11 @@ class B200Engine(Engine):
         self._pin_i = 0
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.side_stream = torch.cuda.Stream(device=dev)
+        # The step's kernels each want most of the machine, so whichever launches first holds the SMs.  The main chain
+        # (forward, dgrads, conv1 wgrad) IS the critical path: it is captured on a high-priority stream, so its blocks are
+        # placed first whenever SM resources free up, and the weight-gradient / optimizer / collective branches fill in
+        # behind it (kernel nodes of a graph inherit the priority of the stream they were captured on).
+        self.main_stream = torch.cuda.Stream(device=dev, priority=-5) if _env_flag("B200DP_PRIO") else None
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._warm: set = set()
         self.dist: Optional[DistributedAdam] = None
@@ -235,7 +251,7 @@ class B200Engine(Engine):
 
     def _plan_comm(self) -> None:
         """Static bucket plan: which ranges each comm kernel reduces, and with which algorithm."""
-        buckets = plan_arena_buckets(self.spec, [["dense.bias", "out."], ["dense.kernel"], ["conv1.", "conv2."]])
+        buckets = plan_arena_buckets(self.spec, [["dense.bias", "out."], ["dense.kernel"], ["conv1."], ["conv2."]])
         self.reduce = bool(self.dist is not None and self.n > 1)
         adasum = self.reduce and self.dist.op is C.Adasum
         forced = self.dist.algo if self.dist else None
@@ -247,6 +263,29 @@ class B200Engine(Engine):
                 self._sharded_ranges.append((b.start, b.numel))
             return (b.start, b.numel, algo, 1)
         by = {b.name: b for b in buckets}
+        # Fused dense path (default): no gradient buffer and no allreduce for dense.kernel (98 % of the parameters) at all.
+        # Every rank gathers the peers' dz and its own feature slice of their activations, runs the wgrad GEMM over the
+        # GLOBAL batch for the rows it owns, applies Adam in the GEMM epilogue and stores the bf16 weights into every rank.
+        # The small tensors are reduced by two one-shot kernels: conv2/out/dense.bias underneath the rest of backward, and
+        # conv1 (832 values) as the only exposed collective of the step.  B200DP_DENSE_FUSED=0 or a forced algorithm
+        # (oneshot/twoshot/nvls) brings back the gradient-buffer paths.
+        dk0 = self.spec.param("dense.kernel")
+        self.dense_fused = bool(self.tc_dense and self.tc_conv and not adasum and (self.reduce or self.n == 1) and self.adam is not None
+                                and forced in (None, "auto") and not os.environ.get("B200DP_ALLREDUCE_ALGO")
+                                and self.F % (8 * self.n) == 0 and self.D % 64 == 0 and dk0.offset % 4 == 0
+                                and _env_flag("B200DP_DENSE_FUSED"))
+        if self.dense_fused:
+            if self.n > 1:
+                self._sharded_ranges.append((dk0.offset, dk0.numel))
+            self.gemm_rs = False
+            self.comm_dense = []
+            one = lambda b: (b.start, b.numel, 0, 1)
+            self.comm_rest = [one(by["conv2."]), one(by["dense.bias+out."])]
+            self.comm_tail = [one(by["conv1."])]
+            self.adasum = False
+            self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
+            return
+        self.comm_tail = []
         self.comm_dense = [rng(by["dense.kernel"])]
         # dense.kernel's gradient is produced by plain stores (GEMM epilogue), never accumulated: nothing to clear
         self.comm_dense = [(r[0], r[1], r[2], 0) for r in self.comm_dense]
@@ -259,7 +298,7 @@ class B200Engine(Engine):
                             and _env_flag("B200DP_GEMM_RS"))
         if self.gemm_rs:
             self.comm_dense = [(dk.offset, dk.numel, 3, 1)]
-        self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1.+conv2."])]
+        self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1."]), rng(by["conv2."])]
         self.adasum = adasum
         self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
 
@@ -346,7 +385,7 @@ class B200Engine(Engine):
             # dense bucket: gradient complete (side 1) and W no longer read (dgrad done)
             s1.wait_event(ev_dgrad)
             with torch.cuda.stream(s1):
-                self._comm(0, self.comm_dense, par)
+                self._timed(self._comm, 0, self.comm_dense, par)
         ev_s1 = torch.cuda.Event()
         ev_s1.record(s1)
         gscale = 1.0 / (1.0 - self.feat_drop) if (self.dropout and self.feat_drop > 0) else 1.0
@@ -375,10 +414,104 @@ class B200Engine(Engine):
         if self.adasum:
             self._adasum_update(par)
         else:
-            self._comm(1, self.comm_rest, par)
+            self._timed(self._comm, 1, self.comm_rest, par)
+
+    def _timed(self, fn, *a, **k) -> None:
+        """Run a collective kernel launch; when this step samples timings, bracket it with events on its stream."""
+        if not self._timing_now:
+            fn(*a, **k)
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(*a, **k)
+        e1.record()
+        self._comm_events.append((e0, e1))
+
+    def last_comm_ms(self) -> Optional[float]:
+        """Device time of the collective kernels of the last sampled step (gather/allreduce+Adam kernels summed; the
+        barrier waits inside them included), or None when no step was sampled yet."""
+        if not self._comm_events:
+            return None
+        self._comm_events[-1][1].synchronize()
+        return float(sum(a.elapsed_time(b) for a, b in self._comm_events))
+
+    def _dense_wgrad_adam(self, B: int) -> None:
+        """dense.kernel: gather (n > 1) -> wgrad GEMM over the global batch -> Adam in the epilogue -> bf16 weights to all."""
+        n, T4 = self.n, self.T * 4
+        dk = self.spec.param("dense.kernel")
+        Fs = self.F // n
+        if n > 1:
+            self._timed(K.allgather_acts, self.arena.h, 3, 16, self.seg_act, self.ACT_A2, self.seg_act, self.ACT_DZ, self.seg_act,
+                        self.ACT_A2G, self.ACT_DZG, B, self.F, self.D)
+            A = self.arena.view(self.seg_act, self.ACT_A2G, n * B * Fs, bf16).view(n * B, Fs)
+            Bm = self.arena.view(self.seg_act, self.ACT_DZG, n * B * self.D, bf16).view(n * B, self.D)
+        else:
+            A, Bm = self.a2[:B].view(B, self.F), self.dz[:B]
+        tiles128 = -(-Fs // 128) * (self.D // 128) if self.D % 128 == 0 else 0
+        bn = 128 if tiles128 >= 96 else 64
+        K.gemm_tc_wgrad_adam(self.arena.h, A, Bm, Fs, self.D, n * B, Fs, self.D, state_seg=self.seg_state, master_off=0,
+                             m_off=T4, v_off=2 * T4, w16_seg=self.seg_w16, w16_off=0, ctrl_seg=self.seg_ctrl,
+                             step_off=CTRL_STEP, hyper_off=CTRL_HYPER, param_start=dk.offset, row0=self.rank * Fs,
+                             gscale=self.scale, block_n=bn)
+
+    def _backward_fused(self, B: int, par: int) -> None:
+        """Backward with the fused dense path (see _plan_comm), three streams captured as graph branches:
+
+            main : dense dgrad -> unpool (+conv2 bias grad) -> conv2 dgrad -> conv1 wgrad -> [join] -> comm(conv1): the only
+                   collective whose latency the step sees
+            side1: head wgrad ; after dgrad: gather dz/a2 over NVLink -> dense wgrad GEMM + Adam + weight push
+            side2: conv2 wgrad ; comm(conv2, out, dense.bias) underneath conv2 dgrad / conv1 wgrad
+        """
+        w, g = self.w16, self.grads[par]
+        main = torch.cuda.current_stream()
+        s1, s2 = self.comm_stream, self.side_stream
+        wd = self.pv("dense.kernel", w)
+        dpool = self.dpool[:B].view(B, self.F)
+        ev_head = torch.cuda.Event()
+        ev_head.record(main)
+        s1.wait_event(ev_head)
+        with torch.cuda.stream(s1):
+            K.head_wgrad(self.h[:B], self.dz[:B], self.dlogits[:B], self.pv("out.kernel", g), self.pv("out.bias", g),
+                         self.pv("dense.bias", g))
+            ev_hw = torch.cuda.Event()
+            ev_hw.record(s1)
+        K.gemm_tc(self.dz[:B], wd, dpool, B, self.F, self.D, out_mode=1, block_n=32)
+        ev_dgrad = torch.cuda.Event()
+        ev_dgrad.record(main)
+        s1.wait_event(ev_dgrad)          # W is no longer read locally; arriving at the gather's barrier tells the peers so
+        with torch.cuda.stream(s1):
+            self._dense_wgrad_adam(B)
+            ev_s1 = torch.cuda.Event()
+            ev_s1.record(s1)
+        gscale = 1.0 / (1.0 - self.feat_drop) if (self.dropout and self.feat_drop > 0) else 1.0
+        K.unpool_relu_bwd(self.dpool[:B], self.a2[:B], self.am2[:B], self.dy2[:B], self.pv("conv2.bias", g), gscale=gscale)
+        ev_dy = torch.cuda.Event()
+        ev_dy.record(main)
+        k2 = self.pv("conv2.kernel", w)
+        s2.wait_event(ev_dy)
+        with torch.cuda.stream(s2):
+            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
+        K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B], pad=self.PAD2)
+        ev_dg2 = torch.cuda.Event()
+        ev_dg2.record(main)
+        with torch.cuda.stream(s2):
+            s2.wait_event(ev_hw)
+            s2.wait_event(ev_dg2)        # the update rewrites the conv2 weights the dgrad above is reading
+            self._timed(self._comm, 1, self.comm_rest, par, nblocks=32, nthreads=128)
+            ev_s2 = torch.cuda.Event()
+            ev_s2.record(s2)
+        if self.keras:
+            K.conv1_valid_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        else:
+            K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        main.wait_event(ev_s2)
+        main.wait_event(ev_s1)
+        # every peer reaches this kernel's barrier after its own weight pushes: passing it means the new dense weights of
+        # ALL owners have landed here, and that nobody still reads this rank's a2/dz
+        self._timed(self._comm, 2, self.comm_tail, par, nblocks=1, nthreads=256)
 
     def _comm(self, channel: int, ranges, par: int, *, reduce: Optional[bool] = None, grad_off: Optional[int] = None,
-              scale: Optional[float] = None) -> None:
+              scale: Optional[float] = None, nblocks: Optional[int] = None, nthreads: int = 512) -> None:
         T4 = self.T * 4
         red = self.reduce if reduce is None else reduce
         sc = self.scale if scale is None else scale
@@ -393,9 +526,9 @@ class B200Engine(Engine):
                     float(sc), r[0], r[1], r[3], ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "fused_nvls")
         if not p2p:
             return
-        nb = self.comm_blocks if sum(r[1] for r in p2p) >= (1 << 20) else 32
+        nb = nblocks or (self.comm_blocks if sum(r[1] for r in p2p) >= (1 << 20) else 32)
         self.arena.fused_allreduce_adam(
-            channel=channel, nblocks=nb, nthreads=512, reduce=red,
+            channel=channel, nblocks=nb, nthreads=nthreads, reduce=red,
             grad_seg=self.seg_grad, grad_cur_off=cur, grad_other_off=(1 - par) * T4,
             state_seg=self.seg_state, master_off=0, m_off=T4, v_off=2 * T4, w16_seg=self.seg_w16, w16_off=0,
             ctrl_seg=self.seg_ctrl, step_off=CTRL_STEP, hyper_off=CTRL_HYPER, scale=sc, ranges=p2p)
@@ -421,7 +554,10 @@ class B200Engine(Engine):
         if nvtx:
             torch.cuda.nvtx.range_pop()
             torch.cuda.nvtx.range_push("b200dp.backward+allreduce+adam")
-        self._backward_and_update(B, par)
+        if self.dense_fused:
+            self._backward_fused(B, par)
+        else:
+            self._backward_and_update(B, par)
         if nvtx:
             torch.cuda.nvtx.range_pop()
         self.launches_per_step = K.LAUNCHES[0] - c0
@@ -461,6 +597,18 @@ class B200Engine(Engine):
         if overlap:
             main.wait_event(self._in_ready[par])
 
+    def stage_device_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """Device-resident batch ([B,784] fp32, [B] int32) into the next step's input buffer, copied on the copy stream
+        underneath the step that is still running (the two input buffers alternate with the gradient-buffer parity)."""
+        par = self.global_step & 1
+        cs = self.copy_stream
+        cs.wait_event(self._buf_free[par])
+        with torch.cuda.stream(cs):
+            self._xs[par][:x.shape[0]].copy_(x, non_blocking=True)
+            self._ys[par][:x.shape[0]].copy_(y, non_blocking=True)
+            self._in_ready[par].record(cs)
+        torch.cuda.current_stream().wait_event(self._in_ready[par])
+
     def train_step(self, x, y) -> StepResult:
         if self.adam is None:
             raise RuntimeError("no optimizer set; pass optimizer=Adam(...) or compile() the model")
@@ -470,11 +618,21 @@ class B200Engine(Engine):
         self._stage_inputs(x, y, B, overlap=True)
         par = self.global_step & 1
         key = (B, par)
-        if self.use_graph and key in self._warm:
+        if self.sample_comm_timing:
+            # one eagerly launched step with events around its collectives (the log line's allreduce_ms)
+            self.sample_comm_timing = False
+            self._comm_events = []
+            self._timing_now = True
+            try:
+                self._train_graphable(B, par)
+            finally:
+                self._timing_now = False
+            self._warm.add(key)
+        elif self.use_graph and key in self._warm:
             g = self._graphs.get(key)
             if g is None:
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
+                with torch.cuda.graph(g, stream=self.main_stream):
                     self._train_graphable(B, par)
                 self._graphs[key] = g
                 # capture does not execute: the step still has to run
@@ -501,7 +659,7 @@ class B200Engine(Engine):
             g = self._graphs.get(key)
             if g is None:
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
+                with torch.cuda.graph(g, stream=self.main_stream):
                     self._train_graphable(B, par)
                 self._graphs[key] = g
             g.replay()
@@ -559,6 +717,20 @@ class B200Engine(Engine):
                     self.arena.pull_from_peer(self.seg_state, (base + st + lo) * 4, (hi - lo) * 4, r)
         torch.cuda.synchronize()
         self._shards_stale = False
+
+    def finalize(self) -> None:
+        """Collective, at the end of training: every rank brings its copy of the owner-sharded fp32 state up to date
+        (all-gather of the slices over NVLink), so whatever rank 0 saves or exports afterwards touches local memory only
+        and no rank reads a peer that may already have shut down."""
+        if self.n > 1 and self._sharded_ranges and self._shards_stale and _w.is_initialized():
+            torch.cuda.synchronize()
+            for (st, ln) in self._sharded_ranges:
+                for base in (0, self.T, 2 * self.T):
+                    self.arena.allgather_slices_(self.seg_state, (base + st) * 4, ln, nblocks=32)
+            torch.cuda.synchronize()
+            self._shards_stale = False
+        if self.n > 1 and _w.is_initialized():
+            _w.barrier()
 
     def state(self) -> Dict[str, Any]:
         self._gather_sharded()

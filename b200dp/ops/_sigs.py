@@ -15,6 +15,9 @@ _SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_comm_pad_bytes": (SZ, []),
     "b200_comm_create": (I, [I, I, I, C.POINTER(P)]),
+    "b200_comm_rank": (I, [P]),
+    "b200_comm_nranks": (I, [P]),
+    "b200_comm_is_emulated": (I, [P]),
     "b200_comm_set_timeout_ms": (I, [P, D]),
     "b200_comm_set_debug_skew_ns": (I, [P, C.c_uint]),
     "b200_comm_seg_alloc": (I, [P, SZ, PI, P]),
@@ -26,6 +29,8 @@ _SIGS = {
     "b200_broadcast": (I, [P, I, I, I, I, I, SZ, I, SZ, LL, P]),
     "b200_allgather_slices": (I, [P, I, I, I, I, SZ, LL, P]),
     "b200_comm_pull_from_peer": (I, [P, I, SZ, SZ, I, P]),
+    "b200_allgather_acts": (I, [P, I, I, I, SZ, I, SZ, I, SZ, SZ, I, I, I, P]),
+    "b200_gemm_tc_wgrad_adam": (I, [P, P, P, I, I, I, I, I, I, SZ, SZ, SZ, I, SZ, I, SZ, SZ, LL, I, I, F, I, P]),
     "b200_nvls_supported": (I, []),
     "b200_comm_mcseg_alloc": (I, [P, SZ, PI, PI, PI, C.POINTER(SZ)]),
     "b200_comm_mcseg_open": (I, [P, I, PI, I]),

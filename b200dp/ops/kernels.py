@@ -182,6 +182,22 @@ def gemm_tc_reduce_scatter(comm_handle, A, Bm, c_seg: int, c_off: int, nranks: i
           "gemm_tc_reduce_scatter")
 
 
+def allgather_acts(comm_handle, channel: int, nblocks: int, act_seg: int, act_off: int, dz_seg: int, dz_off: int, out_seg: int,
+                   act_out_off: int, dz_out_off: int, B: int, F: int, D: int):
+    """Every rank's dz [B,D] and this rank's column slice of every rank's a2 [B,F] -> local [n*B,D] / [n*B,F/n]."""
+    check(lib().b200_allgather_acts(comm_handle, channel, nblocks, act_seg, act_off, dz_seg, dz_off, out_seg, act_out_off,
+                                    dz_out_off, B, F, D, _stream()), "allgather_acts")
+
+
+def gemm_tc_wgrad_adam(comm_handle, A, Bm, M: int, N: int, K: int, lda: int, ldb: int, *, state_seg: int, master_off: int, m_off: int,
+                       v_off: int, w16_seg: int, w16_off: int, ctrl_seg: int, step_off: int, hyper_off: int, param_start: int,
+                       row0: int, as_rank: int = -1, gscale: float = 1.0, block_n: int = 128):
+    """Dense wgrad over the global batch with Adam in the epilogue; new bf16 weights go to every rank (see b200dp.h)."""
+    check(lib().b200_gemm_tc_wgrad_adam(comm_handle, _p(_chk(A, bf16, "A")), _p(_chk(Bm, bf16, "B")), M, N, K, lda, ldb, state_seg,
+                                        master_off, m_off, v_off, w16_seg, w16_off, ctrl_seg, step_off, hyper_off, param_start,
+                                        row0, as_rank, float(gscale), block_n, _stream()), "gemm_tc_wgrad_adam")
+
+
 def conv_tc_fwd(inp, w, bias, out, argmax=None, *, relu=True, pool=False, pad: Optional[int] = None):
     """``pad=None``: SAME (k//2); ``pad=0``: VALID.  ``out`` is [B, H+2p-k+1, W+2p-k+1, Co] (halved when pooling)."""
     B, H, W, Ci = inp.shape

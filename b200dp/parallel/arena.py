@@ -58,7 +58,14 @@ class SymmetricArena:
     def create(cls, world, nbytes: Optional[int] = None) -> "SymmetricArena":
         h = ctypes.c_void_p()
         K.check(K.lib().b200_comm_create(world.rank, world.size, 0, ctypes.byref(h)), "comm_create")
-        return cls(h, world.rank, world.size, False, world.device)
+        self = cls(h, world.rank, world.size, False, world.device)
+        # How long a kernel spins at a peer-memory barrier before it reports the missing rank and traps.  Peers wait
+        # there while rank 0 alone writes a checkpoint or runs an export, so the default sits well above such pauses.
+        ms = os.environ.get("B200DP_COLLECTIVE_TIMEOUT_MS")
+        if ms is None and os.environ.get("B200DP_COLLECTIVE_TIMEOUT_S"):
+            ms = float(os.environ["B200DP_COLLECTIVE_TIMEOUT_S"]) * 1e3
+        self.set_timeout_ms(float(ms) if ms is not None else 300e3)
+        return self
 
     @classmethod
     def emulated(cls, nranks: int, device: Optional[torch.device] = None) -> "SymmetricArena":
@@ -212,7 +219,8 @@ class SymmetricArena:
         return nb, 512
 
     def _stage_chunks(self, numel: int) -> Iterable[Tuple[int, int]]:
-        self._ensure_staging(min(numel, 1 << 24))
+        # never ask for more than one chunk: a tensor above the staging capacity is what this loop exists for
+        self._ensure_staging(min(numel, self._staging_elems) if self._staging is not None else min(numel, 1 << 24))
         off = 0
         while off < numel:
             n = min(self._staging_elems, numel - off)

@@ -113,10 +113,25 @@ def init(device: Optional[str] = None, *, timeout_s: float = 600.0, arena_bytes:
             w.backend = "gloo"
         _WORLD = w
         if size > 1 and w.is_cuda:
+            _require_single_node(w)
             from ..parallel.arena import SymmetricArena
             w.arena = SymmetricArena.create(w, nbytes=arena_bytes)
             w.backend = "p2p"
         return w
+
+
+def _require_single_node(w: World) -> None:
+    """The CUDA data plane maps every peer's memory with CUDA IPC over one NVSwitch domain, so all ranks must share
+    a host and fit the kernels' rank table.  Checked here so a multi-pod launch fails with a sentence instead of an
+    opaque cudaIpcOpenMemHandle error (set B200DP_FORCE_CPU=1 for the gloo path across pods)."""
+    hosts = [None] * w.size
+    dist.all_gather_object(hosts, w.host)
+    if len(set(hosts)) != 1:
+        raise RuntimeError(f"b200dp: the GPU data plane is single-node (one NVSwitch domain), but ranks run on {sorted(set(hosts))}; "
+                           f"use one worker pod with all GPUs, or B200DP_FORCE_CPU=1 / --cpu for the gloo path")
+    max_ranks = 8                    # B200_MAX_RANKS in include/b200dp.h
+    if w.size > max_ranks:
+        raise RuntimeError(f"b200dp: world size {w.size} exceeds the {max_ranks} ranks the peer-memory kernels address")
 
 
 def shutdown() -> None:
@@ -126,6 +141,15 @@ def shutdown() -> None:
         if w is None:
             return
         if w.arena is not None:
+            # Peers keep each other's segments mapped (CUDA IPC) and rank 0 may still be pulling sharded optimizer
+            # state out of them for its final checkpoint/export: nobody frees until everybody is done.  A rank that
+            # died never arrives; the launcher's fail-fast teardown (or the gloo timeout) ends the wait.
+            try:
+                torch.cuda.synchronize()
+                if dist.is_initialized():
+                    dist.barrier()
+            except Exception:
+                pass
             try:
                 w.arena.close()
             except Exception:

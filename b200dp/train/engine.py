@@ -63,6 +63,9 @@ class Engine:
     def load_state(self, tensors: Dict[str, torch.Tensor], meta: Dict[str, Any]) -> None: ...
     def broadcast_state(self, root_rank: int = 0) -> None: ...
 
+    def finalize(self) -> None:
+        """Collective hook at the end of training (session exit / end of fit); engines with rank-sharded state gather it."""
+
     # shared helpers ---------------------------------------------------------
     def set_lr(self, lr: float) -> None:
         """Change the learning rate without rebuilding anything (LR schedules / warm-up callbacks)."""

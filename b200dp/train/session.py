@@ -67,12 +67,25 @@ class LoggingTensorHook(SessionRunHook):
         self.tensors = tuple(tensors) if tensors else ("step", "loss")
         self._iter = 0
 
+    def before_run(self, session):
+        # the step that will be logged also samples the device time of its collectives (engines that can: CUDA events
+        # around the comm kernels of one eagerly launched step)
+        if self._iter % self.every == 0 and hasattr(session.engine, "sample_comm_timing"):
+            session.engine.sample_comm_timing = True
+
     def after_run(self, session, result):
         if self._iter % self.every == 0:
-            extra: Dict[str, Any] = {}
+            extra: Dict[str, Any] = {"batch": int(result.n)}
             if "accuracy" in self.tensors:
                 extra["accuracy"] = result.accuracy()
-            get_logger().step(session.engine.global_step, result.loss_value(), **extra)
+            eng = session.engine
+            if getattr(eng, "adam", None) is not None:
+                extra["lr"] = float(eng.adam.lr)
+            ms = getattr(eng, "last_comm_ms", None)
+            ms = ms() if callable(ms) else ms
+            if ms is not None:
+                extra["allreduce_ms"] = round(float(ms), 4)
+            get_logger().step(eng.global_step, result.loss_value(), **extra)
         self._iter += 1
 
 
@@ -230,6 +243,9 @@ class MonitoredTrainingSession:
                 get_logger().warning("timeline_save_failed", error=str(e))
         try:
             if exc_type is None:
+                # every rank leaves the loop at the same global step: a collective point.  Sharded optimizer state is
+                # gathered everywhere before rank 0's final save, which then needs no peer (peers may shut down first).
+                self.engine.finalize()
                 for h in self.hooks:
                     h.end(self)
             else:

@@ -358,6 +358,9 @@ class Model:
                 if "accuracy" in self.metrics_names:
                     logs["val_accuracy"] = vl[1]
             dt = time.time() - t0
+            # collective point (every rank runs the same epochs): bring rank-sharded optimizer state home everywhere, so
+            # rank-0-only callbacks (ModelCheckpoint) and a later save()/evaluate() never read a peer's memory
+            self.engine.finalize()
             for cb in cbs:
                 cb.on_epoch_end(epoch, logs)
             if verbose:

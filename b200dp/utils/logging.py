@@ -74,7 +74,13 @@ class JsonLogger:
         ``INFO:tensorflow:loss = …, step = … (… sec)`` text form on stderr."""
         now = time.time()
         dt = None if self._last_step_t is None else now - self._last_step_t
-        self._last_step_t = now
+        prev = getattr(self, "_last_step_n", None)
+        self._last_step_t, self._last_step_n = now, int(step)
+        if dt is not None and prev is not None and int(step) > prev:
+            # wall time per step since the previous line (the reference prints the interval: "(x.xxx sec)")
+            fields.setdefault("step_ms", round(dt * 1e3 / (int(step) - prev), 4))
+            if "batch" in fields:
+                fields.setdefault("images_per_sec", round(fields["batch"] * self.size * (int(step) - prev) / max(dt, 1e-9), 1))
         self.info("train_step", step=int(step), loss=float(loss), **fields)
         if self.tf_style and self.level <= 20:
             tail = f" ({dt:.3f} sec)" if dt is not None else ""

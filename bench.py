@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--no-tc", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--adasum", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="--impl standin: capture the whole DDP step (NCCL all-reduce included) in a CUDA graph")
     return ap.parse_args()
 
 
@@ -161,10 +162,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    pxs, pys = list(pool_x.unbind(0)), list(pool_y.unbind(0))
+
     def step_dev(i):
         j = i % pool_n
-        eng.x.copy_(pool_x[j], non_blocking=True)
-        eng.y.copy_(pool_y[j], non_blocking=True)
+        eng.stage_device_batch(pxs[j], pys[j])       # pool -> input buffer on the copy stream, underneath the previous step
         eng.train_step_device(B)
 
     sampler = ClockSampler(dev.index or 0) if rank == 0 else None
@@ -231,8 +233,12 @@ def main():
                                  f"keras128(conv3x3x{eng.C1}-conv3x3x{eng.C2}-pool-dropout0.25-dense{eng.D}-dropout0.5-dense10, ")
                                 + f"{spec.num_params} params)", "global_batch": B * world_size, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world_size}", "optimizer": "Adam(lr=0.001*size) fused into the NVLink allreduce",
-                       "allreduce": {"dense.kernel": ["oneshot", "twoshot", "nvls", "gemm+reduce-scatter fused, then two-shot tail"][eng.comm_dense[0][2]],
-                                     "rest": ["oneshot", "twoshot", "nvls"][eng.comm_rest[1][2]], "wire": "fp32"},
+                       "allreduce": ({"dense.kernel": "none: all-gather of dz + activation slices (bf16) -> wgrad GEMM over the global batch "
+                                                      "-> Adam in the GEMM epilogue -> bf16 weights stored to all ranks",
+                                      "rest": "oneshot (conv2/out/bias underneath backward; conv1 exposed)", "wire": "bf16 activations / fp32 small grads"}
+                                     if eng.dense_fused else
+                                     {"dense.kernel": ["oneshot", "twoshot", "nvls", "gemm+reduce-scatter fused, then two-shot tail"][eng.comm_dense[0][2]],
+                                      "rest": ["oneshot", "twoshot", "nvls"][eng.comm_rest[1][2]], "wire": "fp32"}),
                        "cuda_graph": bool(eng.use_graph), "tcgen05": {"dense": bool(eng.tc_dense), "conv2": bool(eng.tc_conv)},
                        "l2": f"inputs rotate through a {pool_n * B * 784 * 4 / 1e6:.0f} MB device pool (> 126 MB L2); "
                              f"e2e inputs come from pinned host memory every step"},

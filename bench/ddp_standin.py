@@ -1,6 +1,11 @@
 """Stand-in for the reference's Horovod+NCCL(+cuDNN/cuBLAS) stack, which cannot be installed offline
 (SURVEY §0.2-3): the identical CNN / Adam / batch / LR rule in PyTorch eager + DistributedDataParallel
-over NCCL, bf16 autocast, channels-last, fused Adam.  "A path that only calls NCCL" — the baseline."""
+over NCCL, bf16 autocast, channels-last, fused Adam.  "A path that only calls NCCL" — the baseline.
+
+Two forms: the eager loop (DistributedDataParallel, what a user writes first) and ``--graph``: the WHOLE step — forward,
+backward, one NCCL all-reduce of a flat gradient buffer the parameters' .grad fields are views of, the 1/size scale and the
+fused (capturable) Adam — captured once in a CUDA graph and replayed, which removes the host launch latency that dominates
+the eager loop on a model this small.  Every ratio quoted in BASELINE.md uses the faster of the two."""
 import json
 import os
 
@@ -60,7 +65,8 @@ def run(args) -> int:
     torch.backends.cudnn.benchmark = True
     B = args.batch
     model = (KerasNet if getattr(args, "arch", "mnist_cnn") == "keras128" else Net)(args.width).to(dev).to(memory_format=torch.channels_last)
-    net = nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=64, gradient_as_bucket_view=True) if world > 1 else model
+    eager_ddp = world > 1 and not getattr(args, "graph", False)
+    net = nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=64, gradient_as_bucket_view=True) if eager_ddp else model
     opt = torch.optim.Adam(model.parameters(), lr=0.001 * world, fused=True)
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
     pool_n = max(8, int(160e6 // (B * 784 * 4)) + 1)
@@ -74,6 +80,48 @@ def run(args) -> int:
         loss.backward()
         opt.step()
         return loss
+
+    graphed = bool(getattr(args, "graph", False))
+    if graphed:
+        # static buffers + one flat gradient buffer (each p.grad is a view of it: a single all-reduce, no copies)
+        params = [p for p in model.parameters()]
+        flat = torch.zeros(sum(p.numel() for p in params), device=dev)
+        off = 0
+        for p in params:
+            p.grad = flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+        opt = torch.optim.Adam(params, lr=0.001 * world, fused=True, capturable=True)
+        sx = torch.zeros(B, 784, device=dev)
+        sy = torch.zeros(B, dtype=torch.long, device=dev)
+        sloss = torch.zeros((), device=dev)
+
+        def body():
+            flat.zero_()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = F.cross_entropy(model(sx).float(), sy)
+            loss.backward()
+            if world > 1:
+                dist.all_reduce(flat)
+                flat.mul_(1.0 / world)
+            opt.step()
+            sloss.copy_(loss.detach())
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(11):
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        cg = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(cg):
+            body()
+
+        def step(x, y):  # noqa: F811
+            sx.copy_(x, non_blocking=True)
+            sy.copy_(y, non_blocking=True)
+            cg.replay()
+            return sloss
 
     def barrier():
         torch.cuda.synchronize()
@@ -112,7 +160,8 @@ def run(args) -> int:
     ms, ems = float(t[0]), float(t[1])
     if rank == 0:
         print(json.dumps({
-            "metric": "MNIST CNN training throughput (images/sec), device-timed, max over ranks", "impl": "standin",
+            "metric": "MNIST CNN training throughput (images/sec), device-timed, max over ranks",
+            "impl": "standin-graph" if graphed else "standin", "cuda_graph": graphed,
             "note": "stand-in for Horovod+NCCL (reference not installable offline): PyTorch DDP + NCCL + cuDNN/cuBLAS, bf16 autocast",
             "value": round(args.steps * B * world / (ms / 1e3), 1), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",

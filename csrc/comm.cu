@@ -333,6 +333,73 @@ __global__ void __launch_bounds__(512) copy_collective_kernel(const PlainArgs ar
 }
 
 // -------------------------------------------------------------------------------------------
+// All-gather of the dense layer's backward operands (the "allreduce" of the dense weight gradient, turned inside
+// out): rank r collects every rank's dz [B, D] and the column slice r of every rank's flattened activations a2 [B, F]
+// into local [n*B, D] / [n*B, F/n] buffers.  The wgrad GEMM that follows (b200_gemm_tc_wgrad_adam) contracts over the
+// GLOBAL batch, so the cross-rank gradient sum of the rows rank r owns appears in its accumulators without the
+// 12.8 MB gradient ever crossing NVLink: 2.5 MB of activations do instead (N=8).  One barrier: a rank arrives when its
+// own dz/a2 are final AND it no longer reads the old dense weights (the caller orders the launch after its dgrad).
+// -------------------------------------------------------------------------------------------
+struct GatherArgs {
+  int rank, n, channel;
+  PadPtrs pad;
+  const bf16* act[MAXR];      // every rank's a2 [B, F]
+  const bf16* dz[MAXR];       // every rank's dz [B, D]
+  bf16* act_out;              // local [n*B, F/n]
+  bf16* dz_out;               // local [n*B, D]
+  int B, F, D;
+  unsigned long long timeout;
+};
+
+__device__ __forceinline__ uint4 ld_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+template <bool EMU>
+__global__ void __launch_bounds__(256) allgather_acts_kernel(const GatherArgs areal, const GatherArgs* aemu) {
+  const GatherArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+  const int Fs = a.F / a.n;                       // owned feature slice (multiple of 8 elements)
+  const int dz_v = a.B * a.D / 8;                 // 16-byte vectors of one rank's dz
+  const int fs_v = Fs / 8;                        // 16-byte vectors per row of the slice
+  const int act_v = a.B * fs_v;
+  const int per_rank = dz_v + act_v;
+  const long long total = (long long)per_rank * a.n;
+  const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  // four independent 16-byte peer loads in flight per thread
+  for (long long i0 = tid; i0 < total; i0 += 4 * nthr) {
+    uint4 v[4];
+    void* dst[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * nthr;
+      dst[u] = nullptr;
+      if (i < total) {
+        const int pr = (int)(i / per_rank);
+        const int p = (pr + a.rank) % a.n;        // start with the own rank, then walk the peers: spreads the link load
+        const int j = (int)(i % per_rank);
+        if (j < dz_v) {
+          v[u] = ld_u4(reinterpret_cast<const uint4*>(a.dz[p]) + j);
+          dst[u] = reinterpret_cast<uint4*>(a.dz_out) + (size_t)p * dz_v + j;
+        } else {
+          const int k = j - dz_v, b = k / fs_v, c = k % fs_v;
+          v[u] = ld_u4(reinterpret_cast<const uint4*>(a.act[p] + (size_t)b * a.F + (size_t)a.rank * Fs) + c);
+          dst[u] = reinterpret_cast<uint4*>(a.act_out) + (size_t)p * act_v + k;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (dst[u]) *reinterpret_cast<uint4*>(dst[u]) = v[u];
+  }
+}
+
+// -------------------------------------------------------------------------------------------
 // Adasum: log2(N) levels; at level L rank r pairs with r ^ (1<<L).
 //   a' = (1 - a.b/(2|a|^2)) a + (1 - a.b/(2|b|^2)) b      per tensor segment
 // "a" is always the lower rank's vector so both partners compute bit-identical results.
@@ -477,6 +544,10 @@ int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out) {
   *out = c;
   return B200_OK;
 }
+
+int b200_comm_rank(b200_comm_t h) { return ((Comm*)h)->rank; }
+int b200_comm_nranks(b200_comm_t h) { return ((Comm*)h)->n; }
+int b200_comm_is_emulated(b200_comm_t h) { return ((Comm*)h)->emulated ? 1 : 0; }
 
 int b200_comm_set_timeout_ms(b200_comm_t h, double ms) {
   Comm* c = (Comm*)h;
@@ -685,6 +756,39 @@ int b200_comm_pull_from_peer(b200_comm_t h, int seg, size_t off, size_t bytes, i
   if (peer == me || bytes == 0) return B200_OK;
   B200_CHECK(cudaMemcpyAsync(seg_ptr(c, seg, me, off), seg_ptr(c, seg, peer, off), bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   return B200_OK;
+}
+
+// act/dz: (segment, offset) of every rank's a2 [B,F] / dz [B,D] (bf16); act_out/dz_out: (segment, offset) of the local
+// gathered [n*B, F/n] / [n*B, D] buffers.  F must be divisible by 8*nranks, B*D by 8.
+int b200_allgather_acts(b200_comm_t h, int channel, int nblocks, int act_seg, size_t act_off, int dz_seg, size_t dz_off,
+                        int out_seg, size_t act_out_off, size_t dz_out_off, int B, int F, int D, void* stream) {
+  Comm* c = (Comm*)h;
+  B200_REQUIRE(channel >= 0 && channel < MAXCH, "channel %d outside [0, %d)", channel, MAXCH);
+  B200_REQUIRE(nblocks >= 1 && nblocks <= MAXB, "nblocks %d outside [1, %d]", nblocks, MAXB);
+  B200_REQUIRE(B > 0 && F % (8 * c->n) == 0 && (B * D) % 8 == 0, "allgather_acts: F=%d must be a multiple of 8*%d, B*D of 8", F, c->n);
+  int rc;
+  if ((rc = check_seg(c, act_seg, act_off, (size_t)B * F * 2, "act"))) return rc;
+  if ((rc = check_seg(c, dz_seg, dz_off, (size_t)B * D * 2, "dz"))) return rc;
+  if ((rc = check_seg(c, out_seg, act_out_off, (size_t)B * F * 2, "act_out"))) return rc;
+  if ((rc = check_seg(c, out_seg, dz_out_off, (size_t)c->n * B * D * 2, "dz_out"))) return rc;
+  GatherArgs args[MAXR];
+  const int nr = c->emulated ? c->n : 1;
+  for (int k = 0; k < nr; ++k) {
+    const int me = c->emulated ? k : c->rank;
+    GatherArgs& a = args[k];
+    memset(&a, 0, sizeof a);
+    a.rank = me; a.n = c->n; a.channel = channel;
+    fill_pad(c, me, &a.pad);
+    for (int r = 0; r < c->n; ++r) {
+      a.act[r] = (const bf16*)seg_ptr(c, act_seg, r, act_off);
+      a.dz[r] = (const bf16*)seg_ptr(c, dz_seg, r, dz_off);
+    }
+    a.act_out = (bf16*)seg_ptr(c, out_seg, me, act_out_off);
+    a.dz_out = (bf16*)seg_ptr(c, out_seg, me, dz_out_off);
+    a.B = B; a.F = F; a.D = D;
+    a.timeout = c->timeout_cycles;
+  }
+  return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 256, (cudaStream_t)stream);
 }
 
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg) { return (size_t)nblocks * nseg * 3 * sizeof(double); }

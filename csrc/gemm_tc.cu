@@ -72,9 +72,30 @@ struct GemmParams {
   float* peerC[B200_MAX_RANKS];
   int rows_per_owner;
   int bulk_rs;         // out_mode 3: 1 = bulk reduce-stores from a shared-memory staging row, 0 = per-thread 16-byte red.add
+  // out_mode 4 (wgrad GEMM -> Adam): the tile is the cross-rank gradient SUM of rows this rank owns; the epilogue applies
+  // the 1/size scale and the Adam update to the fp32 master weights / moments at flat index param_base + row*ldc + col and
+  // stores the refreshed bf16 weights into every rank's working copy.  The gradient itself is never written anywhere.
+  float* master;
+  float* adam_m;
+  float* adam_v;
+  bf16* w16[B200_MAX_RANKS];
+  int nranks;
+  long long param_base;
+  const int* step_ptr;
+  const double* hyper;   // lr, beta1, beta2, eps, eps_mode (0: TF placement, 1: torch placement)
+  float gscale;
 };
 
-__global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+struct AdamCoefG {
+  float b1, b2, eps, step_size, vscale;
+};
+__device__ __forceinline__ void adam1(float g, float& p, float& m, float& v, const AdamCoefG& c) {
+  m = c.b1 * m + (1.f - c.b1) * g;
+  v = c.b2 * v + (1.f - c.b2) * g * g;
+  p -= c.step_size * m / (sqrtf(v) * c.vscale + c.eps);
+}
+
+__global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -160,8 +181,10 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
     }
   } else {
     // ===== epilogue: TMEM -> registers -> global (thread = one output row, 16 columns per step) =====
-    mbar_wait(tmem_full, 0, 3);
-    tc_fence_after();
+    if (p.out_mode != 4) {    // mode 4 computes its Adam coefficients first and waits for the accumulator afterwards
+      mbar_wait(tmem_full, 0, 3);
+      tc_fence_after();
+    }
     const int q = warp & 3;                         // TMEM lane quarter this warp may touch
     const int row = m0 + q * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -203,6 +226,38 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // staging row may be overwritten now
       }
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    } else if (out_mode == 4) {
+      // wgrad GEMM -> Adam, part 1 (the four TMEM warps): Adam coefficients (fp64 bias corrections from the device step
+      // counter, overlapped with the main loop), then the whole accumulator tile goes TMEM -> shared memory.  The
+      // pipeline stages are free by then (every MMA has retired), so the tile reuses them: row pitch bn floats, 16-byte
+      // columns XOR-swizzled with the row so that this row-per-thread store and the coalesced sweep below are both
+      // conflict-free.  Part 2 (all six warps) follows the role branches.
+      if (warp == 2 && lane == 0) {
+        AdamCoefG* co = reinterpret_cast<AdamCoefG*>(smem + NSTAGE * stage_bytes + 128);
+        const int t = *p.step_ptr;
+        const double lr = p.hyper[0], b1 = p.hyper[1], b2 = p.hyper[2], eps = p.hyper[3];
+        const double bc1 = 1.0 - pow(b1, (double)t), bc2 = 1.0 - pow(b2, (double)t);
+        co->b1 = (float)b1; co->b2 = (float)b2; co->eps = (float)eps;
+        if (p.hyper[4] == 0.0) { co->step_size = (float)(lr * sqrt(bc2) / bc1); co->vscale = 1.f; }
+        else { co->step_size = (float)(lr / bc1); co->vscale = (float)(1.0 / sqrt(bc2)); }
+      }
+      mbar_wait(tmem_full, 0, 3);
+      tc_fence_after();
+      float* tile = reinterpret_cast<float*>(smem);
+      const int rl = q * 32 + lane;
+      const int f4_per_row = bn >> 2;
+      for (int c0 = 0; c0 < bn; c0 += 16) {
+        uint32_t rr[16];
+        tmem_ld_32x16(taddr + c0, rr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c4 = (c0 >> 2) + j;
+          *reinterpret_cast<uint4*>(tile + (size_t)rl * bn + ((c4 ^ (rl & 7)) << 2)) =
+              make_uint4(rr[4 * j], rr[4 * j + 1], rr[4 * j + 2], rr[4 * j + 3]);
+        }
+      }
+      (void)f4_per_row;
     } else {
     uint32_t r[2][16];
     tmem_ld_32x16(taddr, r[0]);
@@ -251,6 +306,47 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
     }
     }
   }
+  if (p.out_mode == 4) {
+    // Part 2: all 192 threads sweep the tile coalesced (consecutive threads = consecutive 16-byte columns of a parameter
+    // row) through master/m/v with 18 independent 16-byte loads in flight per thread — an HBM-bound pass needs ~64 KB
+    // in flight per SM — apply Adam and store fp32 state + the bf16 weights of every rank.
+    __syncthreads();
+    const AdamCoefG co = *reinterpret_cast<const AdamCoefG*>(smem + NSTAGE * stage_bytes + 128);
+    const float* tile = reinterpret_cast<const float*>(smem);
+    const int bn = p.bn, f4_per_row = bn >> 2, total = BM * f4_per_row;
+    const int nr = p.nranks;
+    const float gs = p.gscale;
+    constexpr int U = 6;
+#pragma unroll 1
+    for (int f0 = threadIdx.x; f0 < total; f0 += U * 192) {
+      float4 pp[U], mm[U], vv[U];
+      long long idx[U];
+      bool ok[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int f = f0 + u * 192;
+        const int rl = f / f4_per_row, c4 = f - rl * f4_per_row;
+        const int grow = m0 + rl, col = n0 + c4 * 4;
+        ok[u] = f < total && grow < p.M && col < p.N;
+        idx[u] = p.param_base + (long long)grow * p.ldc + col;
+        if (ok[u]) { pp[u] = ld_f4(p.master + idx[u]); mm[u] = ld_f4(p.adam_m + idx[u]); vv[u] = ld_f4(p.adam_v + idx[u]); }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        const int f = f0 + u * 192;
+        const int rl = f / f4_per_row, c4 = f - rl * f4_per_row;
+        const float4 g = *reinterpret_cast<const float4*>(tile + (size_t)rl * bn + ((c4 ^ (rl & 7)) << 2));
+        adam1(g.x * gs, pp[u].x, mm[u].x, vv[u].x, co); adam1(g.y * gs, pp[u].y, mm[u].y, vv[u].y, co);
+        adam1(g.z * gs, pp[u].z, mm[u].z, vv[u].z, co); adam1(g.w * gs, pp[u].w, mm[u].w, vv[u].w, co);
+        st_f4(p.master + idx[u], pp[u]); st_f4(p.adam_m + idx[u], mm[u]); st_f4(p.adam_v + idx[u], vv[u]);
+        const uint2 w = pack_bf16x4(pp[u]);
+#pragma unroll 1
+        for (int r = 0; r < nr; ++r) *reinterpret_cast<uint2*>(p.w16[r] + idx[u]) = w;
+      }
+    }
+    if (nr > 1) __threadfence_system();   // weights pushed into the peers are visible before this grid completes
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
@@ -258,16 +354,29 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
 
 }  // namespace
 
+struct AdamEpilogue {
+  float* master; float* m; float* v;
+  bf16* w16[B200_MAX_RANKS];
+  int nranks;
+  long long param_base;
+  const int* step_ptr;
+  const double* hyper;
+  float gscale;
+};
+
 static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* peerC, int rows_per_owner, int M, int N, int K, int lda,
-                          int ldb, int ldc, int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream) {
+                          int ldb, int ldc, int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream,
+                          const AdamEpilogue* adam = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: bad shape %dx%dx%d", M, N, K);
-  B200_REQUIRE(out_mode >= 0 && out_mode <= 3, "gemm_tc: out_mode %d", out_mode);
+  B200_REQUIRE(out_mode >= 0 && out_mode <= 4, "gemm_tc: out_mode %d", out_mode);
+  B200_REQUIRE((out_mode == 4) == (adam != nullptr), "gemm_tc: out_mode 4 needs the Adam epilogue arguments");
   B200_REQUIRE(split_k >= 1, "gemm_tc: split_k %d", split_k);
   B200_REQUIRE(split_k == 1 || out_mode >= 2, "gemm_tc: split_k > 1 needs an accumulating out_mode");
   B200_REQUIRE(block_n >= 16 && block_n <= 256 && block_n % 16 == 0, "gemm_tc: block_n %d must be a multiple of 16 in [16,256]", block_n);
   B200_REQUIRE(!b_mn_major || block_n % 64 == 0, "gemm_tc: MN-major B needs block_n %% 64 == 0 (got %d)", block_n);
   B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tc: lda/ldb must be multiples of 8 elements (16 bytes)");
   B200_REQUIRE(ldc % 4 == 0 && ((uintptr_t)C & 15) == 0, "gemm_tc: C must be 16-byte aligned with ldc %% 4 == 0");
+  B200_REQUIRE(out_mode != 4 || (N % 4 == 0 && split_k == 1), "gemm_tc: the Adam epilogue needs N %% 4 == 0 and no split-K");
 
   CUtensorMap tmA, tmB;
   int rc;
@@ -294,6 +403,12 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
   p.rows_per_owner = rows_per_owner > 0 ? rows_per_owner : 1;
   if (peerC)
     for (int r = 0; r < B200_MAX_RANKS; ++r) p.peerC[r] = peerC[r];
+  if (adam) {
+    p.master = adam->master; p.adam_m = adam->m; p.adam_v = adam->v;
+    for (int r = 0; r < B200_MAX_RANKS; ++r) p.w16[r] = adam->w16[r];
+    p.nranks = adam->nranks; p.param_base = adam->param_base; p.step_ptr = adam->step_ptr; p.hyper = adam->hyper;
+    p.gscale = adam->gscale;
+  }
   p.C = C; p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.a_mn = a_mn_major; p.b_mn = b_mn_major; p.out_mode = out_mode; p.bn = block_n;
   p.kb_total = (K + BK - 1) / BK;
@@ -305,6 +420,12 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
   p.tmem_cols = cols;
   p.nstage = p.kb_per_split < MAX_STAGE ? p.kb_per_split : MAX_STAGE;
   if (p.nstage < 2) p.nstage = 2;
+  if (out_mode == 4) {
+    // the accumulator tile (128 x bn fp32) is parked in the stage buffers: two CTAs per SM matter more than pipeline depth
+    // for this memory-bound epilogue, so at most 3 stages, and at least enough bytes for the tile
+    if (p.nstage > 3) p.nstage = 3;
+    while ((size_t)p.nstage * (A_TILE_BYTES + block_n * BK * 2) < (size_t)BM * block_n * 4) ++p.nstage;
+  }
   {
     const char* e = getenv("B200DP_GEMM_RS_BULK");
     p.bulk_rs = (out_mode == 3 && !(e && e[0] == '0')) ? 1 : 0;
@@ -345,4 +466,41 @@ extern "C" int b200_gemm_tc_reduce_scatter(b200_comm_t comm, const void* A, cons
   }
   for (int r = nranks; r < B200_MAX_RANKS; ++r) peers[r] = peers[nranks - 1];
   return gemm_tc_launch(A, B, peers[0], peers, M / nranks, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, 3, 1, block_n, stream);
+}
+
+// Dense-layer weight gradient fused with its optimizer step — and, across ranks, with the gradient "allreduce" itself:
+// A and B hold the activations / upstream gradients of the GLOBAL batch (every rank's rows, gathered by
+// b200_allgather_acts), so D = A^T.B restricted to the rows this rank owns IS the cross-rank gradient sum of those rows,
+// accumulated in fp32 in TMEM in a fixed order.  The epilogue scales it (1/size), applies Adam to the owner's fp32
+// master weights / moments and stores the new bf16 weights into every rank's working copy over NVLink.
+//   A: stored [K, M] (activations of the owned input-feature slice, M contiguous), B: stored [K, N] (dz), K = nranks*batch.
+//   state_seg holds master | m | v at the given byte offsets; element (row, col) of D is parameter
+//   param_start + (row0 + row) * N + col.  w16_seg/w16_off: bf16 working weights (peer-mapped: all ranks are written).
+//   as_rank: -1 = this communicator's rank; an emulated communicator (all ranks on one GPU) names the rank to run as.
+//   The kernel waits on nothing: order it after the gather (and after every reader of the old weights) with streams.
+extern "C" int b200_gemm_tc_wgrad_adam(b200_comm_t comm, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
+                                       int state_seg, size_t master_off, size_t m_off, size_t v_off, int w16_seg, size_t w16_off,
+                                       int ctrl_seg, size_t step_off, size_t hyper_off, long long param_start, int row0,
+                                       int as_rank, float gscale, int block_n, void* stream) {
+  const int nranks = b200_comm_nranks(comm);
+  if (as_rank < 0) as_rank = b200_comm_rank(comm);      // emulated communicators name the rank to run as
+  B200_REQUIRE(as_rank >= 0 && as_rank < nranks, "gemm_tc_wgrad_adam: rank %d outside world of %d", as_rank, nranks);
+  B200_REQUIRE(param_start % 4 == 0 && N % 4 == 0, "gemm_tc_wgrad_adam: parameter range not 16-byte aligned");
+  AdamEpilogue ep;
+  memset(&ep, 0, sizeof ep);
+  char* st = (char*)b200_comm_seg_ptr(comm, state_seg, as_rank);
+  char* ct = (char*)b200_comm_seg_ptr(comm, ctrl_seg, as_rank);
+  B200_REQUIRE(st && ct, "gemm_tc_wgrad_adam: state/ctrl segment not mapped");
+  ep.master = (float*)(st + master_off); ep.m = (float*)(st + m_off); ep.v = (float*)(st + v_off);
+  for (int r = 0; r < nranks; ++r) {
+    char* w = (char*)b200_comm_seg_ptr(comm, w16_seg, r);
+    B200_REQUIRE(w != nullptr, "gemm_tc_wgrad_adam: weight segment %d is not mapped for rank %d", w16_seg, r);
+    ep.w16[r] = (bf16*)(w + w16_off);
+  }
+  ep.nranks = nranks;
+  ep.param_base = param_start + (long long)row0 * N;
+  ep.step_ptr = (const int*)(ct + step_off);
+  ep.hyper = (const double*)(ct + hyper_off);
+  ep.gscale = gscale;
+  return gemm_tc_launch(A, B, ep.master, nullptr, 0, M, N, K, lda, ldb, N, 1, 1, 4, 1, block_n, stream, &ep);
 }

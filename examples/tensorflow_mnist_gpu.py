@@ -28,6 +28,8 @@ parser.add_argument("--checkpoint-dir", default="./checkpoints")
 parser.add_argument("--export-dir", default="./final_model")
 parser.add_argument("--train-samples", default=60000, type=int)
 parser.add_argument("--test-samples", default=10000, type=int)
+parser.add_argument("--resume", action="store_true",
+                    help="continue from the newest epoch checkpoint in --checkpoint-dir (implied when b200run restarts the job)")
 
 
 def main():
@@ -56,13 +58,28 @@ def main():
         callbacks.append(hvd.callbacks.ModelCheckpoint(
             os.path.join(args.checkpoint_dir, "mnist-{epoch}.safetensors"), save_best_only=True))
 
+    # The reference script has no resume path; `b200run --max-restarts` relaunches the job after a rank died, and a relaunch
+    # that began at epoch 0 again would quietly throw the finished epochs away.  Rank 0 reloads the newest epoch checkpoint
+    # (weights, Adam moments, step); the broadcast callback hands it to everyone on the first batch.
+    initial_epoch = 0
+    if args.resume or int(os.environ.get("B200DP_RESTART_COUNT", "0")) > 0:
+        if hvd.rank() == 0 and os.path.isdir(args.checkpoint_dir):
+            import re
+            found = sorted((int(m.group(1)), f) for f in os.listdir(args.checkpoint_dir)
+                           for m in [re.match(r"mnist-(\d+)\.safetensors$", f)] if m)
+            if found:
+                initial_epoch, name = found[-1]
+                model.load_weights(os.path.join(args.checkpoint_dir, name))
+                print(f"resuming from {name} (epoch {initial_epoch})", file=sys.stderr)
+        initial_epoch = hvd.broadcast_object(initial_epoch, 0)
+
     steps_per_epoch = max(1, len(x_train) // (args.batch_size * hvd.size()))
     validation_steps = max(1, len(x_test) // args.batch_size)
     epochs = max(1, args.num_steps // steps_per_epoch)
 
     model.fit(x_train, y_train, batch_size=args.batch_size, epochs=epochs, steps_per_epoch=steps_per_epoch,
               validation_data=(x_test, y_test), validation_steps=validation_steps, callbacks=callbacks,
-              verbose=1 if hvd.rank() == 0 else 0)
+              verbose=1 if hvd.rank() == 0 else 0, initial_epoch=initial_epoch)
 
     if hvd.rank() == 0:
         score = model.evaluate(x_test, y_test, batch_size=args.batch_size, verbose=0)

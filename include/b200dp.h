@@ -28,6 +28,9 @@ const char* b200_last_error(void);
 /* ---- collective runtime (replaces Horovod core + MPI/NCCL ops; horovod/Dockerfile:64-65) ---- */
 size_t b200_comm_pad_bytes(void);
 int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out);
+int b200_comm_rank(b200_comm_t h);
+int b200_comm_nranks(b200_comm_t h);
+int b200_comm_is_emulated(b200_comm_t h);
 int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
 int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns);   /* race hunting: random delay before each barrier arrival */
 int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out /* 64 B or NULL */);
@@ -54,6 +57,11 @@ int b200_allgather_slices(b200_comm_t h, int channel, int nblocks, int nthreads,
 /* one-sided copy of a peer's [off, off+bytes) into the same range of the local segment (rank-0 checkpoint gather,
  * horovod/tensorflow_mnist.py:157-159: only worker 0 saves) */
 int b200_comm_pull_from_peer(b200_comm_t h, int seg, size_t off, size_t bytes, int peer, void* stream);
+/* The dense layer's gradient "allreduce" turned inside out (horovod/tensorflow_mnist.py:133-136 for layers.dense, :65-66):
+ * every rank gathers all ranks' dz [B,D] and its own column slice of all ranks' activations a2 [B,F] (2.5 MB over NVLink at
+ * N=8 instead of the 12.8 MB gradient), then b200_gemm_tc_wgrad_adam contracts over the global batch. */
+int b200_allgather_acts(b200_comm_t h, int channel, int nblocks, int act_seg, size_t act_off, int dz_seg, size_t dz_off,
+                        int out_seg, size_t act_out_off, size_t dz_out_off, int B, int F, int D, void* stream);
 /* NVLS: segments bound to an NVSwitch multicast object (in-switch reduction). Three steps with the
  * caller's control plane in between: alloc (-> POSIX fds to ship to the peers), open (import + add device),
  * [barrier], bind.  A multicast segment is also peer-mapped, so every P2P entry point accepts it. */
@@ -156,6 +164,15 @@ int b200_gemm_tc(const void* A, const void* B, void* C, int M, int N, int K, int
 int b200_gemm_tc_reduce_scatter(b200_comm_t comm, const void* A, const void* B, int c_seg, size_t c_off, int nranks,
                                 int M, int N, int K, int lda, int ldb, int ldc, int a_mn_major, int b_mn_major,
                                 int block_n, void* stream);
+/* Dense wgrad GEMM over the global batch with the optimizer in its epilogue: D = A^T.B (A stored [K,M], B stored [K,N],
+ * K = nranks*batch rows gathered by b200_allgather_acts) is the cross-rank gradient sum of the M rows this rank owns; the
+ * epilogue scales it, applies Adam (horovod/tensorflow_mnist.py:130) to the fp32 master weights/moments in state_seg and
+ * stores the bf16 weights into EVERY rank's w16_seg over NVLink.  Element (row, col) is parameter
+ * param_start + (row0+row)*N + col.  as_rank -1: the communicator's own rank (emulated communicators name one). */
+int b200_gemm_tc_wgrad_adam(b200_comm_t comm, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
+                            int state_seg, size_t master_off, size_t m_off, size_t v_off, int w16_seg, size_t w16_off,
+                            int ctrl_seg, size_t step_off, size_t hyper_off, long long param_start, int row0, int as_rank,
+                            float gscale, int block_n, void* stream);
 /* Implicit-GEMM 5x5/3x3 SAME convolution on tensor cores, taps applied by shifted TMA boxes (no im2col buffer).
  *   mode 0 forward: out = relu(conv(in, w) + bias), optionally followed by maxpool2 (+argmax)
  *   mode 1 dgrad  : din = conv_transpose(dout, w)  */

@@ -44,19 +44,22 @@ def _check(res, np_, algo):
         assert r0["sharded_ranges"] >= 1
     if algo == "gemm_rs":
         assert r0["gemm_rs"] and 3 in r0["algos"], r0           # dense wgrad GEMM fused with its reduce-scatter
+    if algo == "auto":
+        assert r0["dense_fused"] and r0["sharded_ranges"] == 1, r0     # gather -> wgrad GEMM + Adam epilogue -> weight push
+    assert r0["late_state_finite"] and r0["late_state_matches_weights"], r0    # final save after the peers left for shutdown
     if algo == "nvls" and r0.get("nvls_supported"):
         assert r0["engine_nvls"] and 2 in r0["algos"], r0            # the dense bucket really went through the switch
         assert r0["nvls_bcast_used"], r0                                   # and so did the large public broadcasts
 
 
 @pytest.mark.multigpu(2)
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
+@pytest.mark.parametrize("algo", ["auto", "oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_two_gpus(tmp_path, algo):
     _check(_run(2, algo, tmp_path), 2, algo)
 
 
 @pytest.mark.multigpu(2)
-@pytest.mark.parametrize("algo", ["oneshot@keras128", "gemm_rs@keras128"])
+@pytest.mark.parametrize("algo", ["auto@keras128", "oneshot@keras128", "gemm_rs@keras128"])
 def test_two_gpus_keras128(tmp_path, algo):
     """The keras128 family through the same fused allreduce+Adam / GEMM+reduce-scatter kernels (F=9216, D=128)."""
     res = _run(2, algo, tmp_path)

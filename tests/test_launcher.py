@@ -73,6 +73,40 @@ def test_max_restarts_reruns_job(tmp_path):
     assert "restart 1/2" in r.stderr
 
 
+def test_rank_killed_by_signal_is_restarted(tmp_path):
+    """A rank that dies of SIGKILL (what the OOM killer sends) or a native crash is a failure like any other: the job is
+    torn down and restarted from the latest checkpoint.  Only a signal sent to the launcher itself ends the job."""
+    marker = tmp_path / "m"
+    r = _run(["-np", "2", "--max-restarts", "1", "--grace-secs", "1"], f"""
+        import os, signal, time
+        if os.environ["RANK"] == "1" and os.environ["B200DP_RESTART_COUNT"] == "0":
+            os.kill(os.getpid(), signal.SIGKILL)
+        if os.environ["B200DP_RESTART_COUNT"] == "0":
+            time.sleep(30)
+        if os.environ["RANK"] == "0":
+            open({str(marker)!r}, "w").write(os.environ["B200DP_RESTART_COUNT"])
+    """, timeout=60)
+    assert r.returncode == 0, r.stderr
+    assert marker.read_text() == "1"
+    assert "restart 1/1" in r.stderr
+
+
+def test_signal_to_the_launcher_is_not_restarted(tmp_path):
+    import signal, time
+    up = tmp_path / "up"
+    code = f"import os, time; open({str(up)!r} + os.environ['RANK'], 'w').close(); time.sleep(60)"
+    p = subprocess.Popen(RUN + ["-np", "2", "--max-restarts", "3", "--grace-secs", "1", sys.executable, "-c", code],
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    deadline = time.time() + 60
+    while time.time() < deadline and not (os.path.exists(str(up) + "0") and os.path.exists(str(up) + "1")):
+        time.sleep(0.1)                     # the ranks run, so the launcher's own signal handlers are installed
+    time.sleep(0.3)
+    p.send_signal(signal.SIGTERM)
+    out, err = p.communicate(timeout=30)
+    assert p.returncode == 128 + signal.SIGTERM
+    assert "restart" not in err
+
+
 def test_no_command_is_an_error():
     r = subprocess.run(RUN + ["-np", "1"], capture_output=True, text=True)
     assert r.returncode == 2

@@ -78,6 +78,7 @@ res["sharded_ranges"] = len(eng._sharded_ranges)
 res["engine_nvls"] = bool(eng.nvls)
 res["nvls_bcast_used"] = bool(getattr(hvd.world().arena, "_staging_mc", False))
 res["gemm_rs"] = bool(eng.gemm_rs)
+res["dense_fused"] = bool(eng.dense_fused)
 res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
 # rank 0 alone takes a checkpoint (one-sided gather of sharded Adam state) while the others wait at a barrier
@@ -116,5 +117,14 @@ digests = hvd.allgather_object(hashlib.sha256(eng.w16.cpu().view(torch.int16).nu
 res["identical_after_skewed_stress"] = len(set(digests)) == 1
 res["stress_loss_finite"] = bool(np.isfinite(eng.train_step(xs[0, r], ys[0, r]).loss_value()))
 hvd.world().arena.set_debug_skew_ns(0)
+# End of run: the other ranks go straight to shutdown while rank 0 dawdles and only then reads the (sharded) state for
+# its final save.  shutdown() is collective, so the peers' memory is still mapped and valid when rank 0 pulls from it.
+if r == 0:
+    import time
+    time.sleep(1.5)
+    late = eng.state()
+    res["late_state_finite"] = bool(torch.isfinite(late["tensors"]["params"]).all() and torch.isfinite(late["tensors"]["adam_v"]).all())
+    w_from_master = late["tensors"]["params"].to(torch.bfloat16)
+    res["late_state_matches_weights"] = bool(torch.equal(w_from_master, eng.w16.cpu()))
 json.dump(res, open(os.path.join(out_dir, f"r{r}.json"), "w"))
 hvd.shutdown()

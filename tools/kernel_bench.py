@@ -14,6 +14,7 @@ ap.add_argument("--width", type=float, default=1.0)
 ap.add_argument("--reps", type=int, default=20)
 ap.add_argument("--arch", default="mnist_cnn", choices=["mnist_cnn", "keras128"])
 ap.add_argument("--dense-splits", default="", help="comma list: also time the dense forward GEMM at these split-K factors")
+ap.add_argument("--only", default="", help="substring: time only the kernels whose name contains it (short runs under ncu)")
 ap.add_argument("--out", default="gpurun_out/kernel_bench.json")
 a = ap.parse_args()
 hvd.init(device="cuda")
@@ -47,13 +48,21 @@ ops = {
     "conv2_wgrad(tc)": lambda: K.conv_tc_wgrad(e.a1[:B], e.dy2[:B], e.pv("conv2.kernel", g), None, pad=e.PAD2),
     "conv2_dgrad(tc)": lambda: K.conv_tc_dgrad(e.dy2[:B], e.pv("conv2.kernel", w), e.da1[:B], pad=e.PAD2),
     **conv1w,
-    "fused_adam(dense bucket)": lambda: e._comm(0, e.comm_dense, 0),
-    "fused_adam(rest)": lambda: e._comm(1, e.comm_rest, 0),
 }
+if e.dense_fused:
+    ops["dense_wgrad+adam(tc, fused epilogue)"] = lambda: e._dense_wgrad_adam(B)
+    ops["fused_adam(conv2,out,dense.bias)"] = lambda: e._comm(1, e.comm_rest, 0, nblocks=32, nthreads=128)
+    ops["fused_adam(conv1: step tail)"] = lambda: e._comm(2, e.comm_tail, 0, nblocks=1, nthreads=256)
+    del ops["dense_wgrad(tc)"]
+else:
+    ops["fused_adam(dense bucket)"] = lambda: e._comm(0, e.comm_dense, 0)
+    ops["fused_adam(rest)"] = lambda: e._comm(1, e.comm_rest, 0)
 for sp in [int(v) for v in a.dense_splits.split(",") if v]:
     ops[f"dense_fwd split={sp}"] = (lambda sp=sp: K.gemm_tc(a2f, e.pv("dense.kernel", w), e.z[:B], B, e.D, e.F, b_mn_major=True, out_mode=2, split_k=sp, block_n=64))
     if e.D % 128 == 0:
         ops[f"dense_fwd split={sp} bn128"] = (lambda sp=sp: K.gemm_tc(a2f, e.pv("dense.kernel", w), e.z[:B], B, e.D, e.F, b_mn_major=True, out_mode=2, split_k=sp, block_n=128))
+if a.only:
+    ops = {k: v for k, v in ops.items() if a.only in k}
 res = {}
 print(f"{'kernel':28s} {'us/launch':>10s}")
 for name, fn in ops.items():
