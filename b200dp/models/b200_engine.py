@@ -497,7 +497,8 @@ class B200Engine(Engine):
         with torch.cuda.stream(s2):
             s2.wait_event(ev_hw)
             s2.wait_event(ev_dg2)        # the update rewrites the conv2 weights the dgrad above is reading
-            self._timed(self._comm, 1, self.comm_rest, par, nblocks=32, nthreads=128)
+            # one 16-byte column per thread: the kernel is a barrier plus ONE round of peer loads, not a loop of them
+            self._timed(self._comm, 1, self.comm_rest, par, nblocks=128, nthreads=128)
             ev_s2 = torch.cuda.Event()
             ev_s2.record(s2)
         if self.keras:

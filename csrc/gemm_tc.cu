@@ -89,10 +89,17 @@ struct GemmParams {
 struct AdamCoefG {
   float b1, b2, eps, step_size, vscale;
 };
+// The sweep runs on 12 warps per SM, so it is bound by its dependent instruction chain, not by HBM, unless the chain is
+// short: sqrt and reciprocal are the SFU approximations (2 ulp; IEEE sqrtf and '/' expand to ~60 instructions with
+// fix-up branches per element and made this epilogue 3x slower than the memory system allows).  The owner rank computes
+// each weight once and every replica receives that value, so replicas stay bitwise identical whatever the rounding.
 __device__ __forceinline__ void adam1(float g, float& p, float& m, float& v, const AdamCoefG& c) {
-  m = c.b1 * m + (1.f - c.b1) * g;
-  v = c.b2 * v + (1.f - c.b2) * g * g;
-  p -= c.step_size * m / (sqrtf(v) * c.vscale + c.eps);
+  m = fmaf(c.b1, m, (1.f - c.b1) * g);
+  v = fmaf(c.b2, v, (1.f - c.b2) * g * g);
+  float s, r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(v));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(s, c.vscale, c.eps)));
+  p = fmaf(-c.step_size * m, r, p);
 }
 
 __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,

@@ -435,12 +435,12 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
   extern __shared__ float hs[];            // D floats: bf16-rounded h, then (optionally) a copy of W2
   __shared__ float part[8][NC_MAX];
   __shared__ float dl[NC_MAX];
-  pdl_wait();
-  pdl_launch_dependents();
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   // W2 ([D,NC] bf16, 20 KB for the MNIST head) is read twice per row with a stride the coalescer dislikes:
-  // stage it once per block with 16-byte loads and serve both passes from shared memory.
+  // stage it once per block with 16-byte loads and serve both passes from shared memory.  The weights were written by
+  // the previous step's update, long complete (every kernel of the chain passes its own pdl_wait before it lets its
+  // successor start), so the staging runs BEFORE pdl_wait, underneath the tail of the dense GEMM that produces z.
   const bf16* w2p = w2;
   if (stage_w2) {
     bf16* w2s = reinterpret_cast<bf16*>(hs + D);
@@ -451,6 +451,8 @@ __global__ void __launch_bounds__(256) head_fwd_bwd_kernel(float* __restrict__ z
     w2p = w2s;
     __syncthreads();
   }
+  pdl_wait();
+  pdl_launch_dependents();
   const bool drop = training && drop_rate > 0.f;
   const uint32_t step = step_ptr ? (uint32_t)*step_ptr : 0u;
   const uint32_t thresh = (uint32_t)fminf(drop_rate * 4294967296.f, 4294967295.f);

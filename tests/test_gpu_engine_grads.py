@@ -40,6 +40,10 @@ def test_first_step_gradients_match_autograd(monkeypatch, arch, B, fused):
     for p in spec.params:
         a, b = gm[p.offset:p.offset + p.numel], ref[p.offset:p.offset + p.numel]
         rel = ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
-        if rel > 3e-2:
-            bad.append((p.name, round(rel, 4), round((a.norm() / b.norm().clamp_min(1e-12)).item(), 4)))
+        ratio = (a.norm() / b.norm().clamp_min(1e-12)).item()
+        # bf16 activations and upstream gradients put 3-5 % of rounding noise on the small early-layer tensors (measured on
+        # the unfused path); a missing tap, a stale operand or a wrong scale shows up as 10 % and more, or as a norm ratio
+        # away from 1
+        if rel > 7e-2 or abs(ratio - 1.0) > 5e-2:
+            bad.append((p.name, round(rel, 4), round(ratio, 4)))
     assert not bad, f"gradient tensors off (name, relative L2 error, norm ratio): {bad}"
