@@ -441,7 +441,7 @@ class B200Engine(Engine):
         dk = self.spec.param("dense.kernel")
         Fs = self.F // n
         if n > 1:
-            self._timed(K.allgather_acts, self.arena.h, 3, 16, self.seg_act, self.ACT_A2, self.seg_act, self.ACT_DZ, self.seg_act,
+            self._timed(K.allgather_acts, self.arena.h, 3, 148, self.seg_act, self.ACT_A2, self.seg_act, self.ACT_DZ, self.seg_act,
                         self.ACT_A2G, self.ACT_DZG, B, self.F, self.D)
             A = self.arena.view(self.seg_act, self.ACT_A2G, n * B * Fs, bf16).view(n * B, Fs)
             Bm = self.arena.view(self.seg_act, self.ACT_DZG, n * B * self.D, bf16).view(n * B, self.D)
@@ -498,7 +498,7 @@ class B200Engine(Engine):
             s2.wait_event(ev_hw)
             s2.wait_event(ev_dg2)        # the update rewrites the conv2 weights the dgrad above is reading
             # one 16-byte column per thread: the kernel is a barrier plus ONE round of peer loads, not a loop of them
-            self._timed(self._comm, 1, self.comm_rest, par, nblocks=128, nthreads=128)
+            self._timed(self._comm, 1, self.comm_rest, par, nblocks=64, nthreads=256)
             ev_s2 = torch.cuda.Event()
             ev_s2.record(s2)
         if self.keras:

@@ -88,7 +88,8 @@ def run(args) -> int:
         flat = torch.zeros(sum(p.numel() for p in params), device=dev)
         off = 0
         for p in params:
-            p.grad = flat[off:off + p.numel()].view_as(p)
+            # same memory layout as the parameter (conv weights are channels-last): the fused Adam insists on it
+            p.grad = flat[off:off + p.numel()].as_strided(p.size(), p.stride())
             off += p.numel()
         opt = torch.optim.Adam(params, lr=0.001 * world, fused=True, capturable=True)
         sx = torch.zeros(B, 784, device=dev)

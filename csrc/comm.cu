@@ -149,14 +149,30 @@ __device__ __forceinline__ float4 reduce_ptrs(const float* const* ptrs, int n, l
   return s;
 }
 
+// Latency form for the small buckets: all peers' loads are in flight at once (one NVLink round trip instead of two at
+// N=8); the sum still runs in rank order.  Needs ~32 more registers than the 64 the 512-thread kernel may use.
+__device__ __forceinline__ float4 reduce_ptrs_wide(const float* const* ptrs, int n, long long i) {
+  float4 t[MAXR];
+#pragma unroll
+  for (int k = 0; k < MAXR; ++k)
+    if (k < n) t[k] = ld_f4(ptrs[k] + i);
+  float4 s = t[0];
+#pragma unroll
+  for (int k = 1; k < MAXR; ++k)
+    if (k < n) { s.x += t[k].x; s.y += t[k].y; s.z += t[k].z; s.w += t[k].w; }
+  return s;
+}
+
+template <bool WIDE>
 __device__ __forceinline__ float4 reduce_peers(const FusedArgs& a, long long i) {
-  float4 s = reduce_ptrs(a.grad, a.reduce ? a.n : 1, i);
+  float4 s = WIDE ? reduce_ptrs_wide(a.grad, a.reduce ? a.n : 1, i) : reduce_ptrs(a.grad, a.reduce ? a.n : 1, i);
   s.x *= a.scale; s.y *= a.scale; s.z *= a.scale; s.w *= a.scale;
   return s;
 }
 
-template <bool EMU>
-__global__ void __launch_bounds__(512, 2) fused_allreduce_adam_kernel(const FusedArgs areal, const FusedArgs* aemu) {
+// WIDE: blocks of at most 256 threads (the small, latency-bound buckets); otherwise 512 threads x 2 blocks per SM.
+template <bool EMU, bool WIDE>
+__global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kernel(const FusedArgs areal, const FusedArgs* aemu) {
   const FusedArgs& a = EMU ? aemu[blockIdx.y] : areal;
   const int bid = blockIdx.x;
   const long long tid = (long long)bid * blockDim.x + threadIdx.x;
@@ -194,7 +210,7 @@ __global__ void __launch_bounds__(512, 2) fused_allreduce_adam_kernel(const Fuse
       for (long long q = tid; q < nq; q += nthr) {
         const long long i = rg.start + q * 4;
         float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
-        const float4 g = reduce_peers(a, i);
+        const float4 g = reduce_peers<WIDE>(a, i);
         adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
         adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
         st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
@@ -216,7 +232,7 @@ __global__ void __launch_bounds__(512, 2) fused_allreduce_adam_kernel(const Fuse
           g = ld_f4(a.grad[a.rank] + i);
           g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
         } else {
-          g = reduce_peers(a, i);
+          g = reduce_peers<WIDE>(a, i);
         }
         float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
         adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
@@ -358,7 +374,7 @@ __device__ __forceinline__ uint4 ld_u4(const void* p) {
 }
 
 template <bool EMU>
-__global__ void __launch_bounds__(256) allgather_acts_kernel(const GatherArgs areal, const GatherArgs* aemu) {
+__global__ void __launch_bounds__(128, 8) allgather_acts_kernel(const GatherArgs areal, const GatherArgs* aemu) {
   const GatherArgs& a = EMU ? aemu[blockIdx.y] : areal;
   const int bid = blockIdx.x;
   uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
@@ -371,31 +387,41 @@ __global__ void __launch_bounds__(256) allgather_acts_kernel(const GatherArgs ar
   const int per_rank = dz_v + act_v;
   const long long total = (long long)per_rank * a.n;
   const long long tid = (long long)bid * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
-  // four independent 16-byte peer loads in flight per thread
-  for (long long i0 = tid; i0 < total; i0 += 4 * nthr) {
-    uint4 v[4];
-    void* dst[4];
+  // A peer load takes ~3 us over NVLink, so the copy is as fast as the bytes it keeps in flight: eight independent
+  // 16-byte loads per thread, 128-thread blocks of <= 64 registers (8 K registers: they fit on an SM beside a
+  // convolution CTA), one block per SM -> 2.4 MB in flight, the 2.9 MB gather of the 8-rank MNIST step in ~two round trips.
+  constexpr int UG = 8;
+  for (long long i0 = tid; i0 < total; i0 += UG * nthr) {
+    uint4 v[UG];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < UG; ++u) {
       const long long i = i0 + u * nthr;
-      dst[u] = nullptr;
       if (i < total) {
         const int pr = (int)(i / per_rank);
         const int p = (pr + a.rank) % a.n;        // start with the own rank, then walk the peers: spreads the link load
         const int j = (int)(i % per_rank);
         if (j < dz_v) {
           v[u] = ld_u4(reinterpret_cast<const uint4*>(a.dz[p]) + j);
-          dst[u] = reinterpret_cast<uint4*>(a.dz_out) + (size_t)p * dz_v + j;
         } else {
           const int k = j - dz_v, b = k / fs_v, c = k % fs_v;
           v[u] = ld_u4(reinterpret_cast<const uint4*>(a.act[p] + (size_t)b * a.F + (size_t)a.rank * Fs) + c);
-          dst[u] = reinterpret_cast<uint4*>(a.act_out) + (size_t)p * act_v + k;
         }
       }
     }
+    // destinations are recomputed after the loads were issued: eight live 64-bit pointers would push the kernel past
+    // the 64 registers that let its blocks sit beside a convolution CTA
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (dst[u]) *reinterpret_cast<uint4*>(dst[u]) = v[u];
+    for (int u = 0; u < UG; ++u) {
+      const long long i = i0 + u * nthr;
+      if (i < total) {
+        const int pr = (int)(i / per_rank);
+        const int p = (pr + a.rank) % a.n;
+        const int j = (int)(i % per_rank);
+        uint4* dst = j < dz_v ? reinterpret_cast<uint4*>(a.dz_out) + (size_t)p * dz_v + j
+                              : reinterpret_cast<uint4*>(a.act_out) + (size_t)p * act_v + (j - dz_v);
+        *dst = v[u];
+      }
+    }
   }
 }
 
@@ -683,7 +709,10 @@ int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthre
     for (int i = 0; i < nranges; ++i) a.ranges[i] = Range{range_start[i], range_numel[i], range_algo[i], range_zero_other[i]};
     a.timeout = c->timeout_cycles;
   }
-  return launch_ranked(c, args, fused_allreduce_adam_kernel<false>, fused_allreduce_adam_kernel<true>, nblocks, nthreads,
+  if (nthreads <= 256)
+    return launch_ranked(c, args, fused_allreduce_adam_kernel<false, true>, fused_allreduce_adam_kernel<true, true>, nblocks, nthreads,
+                         (cudaStream_t)stream);
+  return launch_ranked(c, args, fused_allreduce_adam_kernel<false, false>, fused_allreduce_adam_kernel<true, false>, nblocks, nthreads,
                        (cudaStream_t)stream);
 }
 
@@ -788,7 +817,7 @@ int b200_allgather_acts(b200_comm_t h, int channel, int nblocks, int act_seg, si
     a.B = B; a.F = F; a.D = D;
     a.timeout = c->timeout_cycles;
   }
-  return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 256, (cudaStream_t)stream);
+  return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 128, (cudaStream_t)stream);
 }
 
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg) { return (size_t)nblocks * nseg * 3 * sizeof(double); }

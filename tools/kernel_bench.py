@@ -51,7 +51,7 @@ ops = {
 }
 if e.dense_fused:
     ops["dense_wgrad+adam(tc, fused epilogue)"] = lambda: e._dense_wgrad_adam(B)
-    ops["fused_adam(conv2,out,dense.bias)"] = lambda: e._comm(1, e.comm_rest, 0, nblocks=128, nthreads=128)
+    ops["fused_adam(conv2,out,dense.bias)"] = lambda: e._comm(1, e.comm_rest, 0, nblocks=64, nthreads=256)
     ops["fused_adam(conv1: step tail)"] = lambda: e._comm(2, e.comm_tail, 0, nblocks=1, nthreads=256)
     del ops["dense_wgrad(tc)"]
 else:
