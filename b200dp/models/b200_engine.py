@@ -66,6 +66,29 @@ class _LazyScalar:
         return self._get()
 
 
+class _HostScalar:
+    """A step's loss / correct count in the pinned host ring the step's last kernel writes (no D2H copy in the stream):
+    reading it waits for that step's completion event, nothing else."""
+
+    def __init__(self, ring: torch.Tensor, slot: int, event: torch.cuda.Event, scale: float = 1.0):
+        self.ring, self.slot, self.event, self.scale, self._v = ring, slot, event, scale, None
+
+    def _get(self):
+        if self._v is None:
+            self.event.synchronize()
+            self._v = self.ring[self.slot].item() * self.scale
+        return self._v
+
+    def __float__(self):
+        return float(self._get())
+
+    def __int__(self):
+        return int(self._get())
+
+    def item(self):
+        return self._get()
+
+
 def _env_flag(name: str, default: str = "1") -> bool:
     return os.environ.get(name, default) not in ("0", "false", "no")
 
@@ -158,6 +181,10 @@ class B200Engine(Engine):
         self.loss_ring = a.view(self.seg_ctrl, CTRL_LOSS_RING, RING, torch.float32)
         self.correct_ring = a.view(self.seg_ctrl, CTRL_CORRECT_RING, RING, torch.int32)
 
+        # host mirror of the two rings: the last kernel of every step stores its slot here (mapped pinned memory)
+        self.host_loss = torch.zeros(RING, dtype=torch.float32).pin_memory()
+        self.host_correct = torch.zeros(RING, dtype=torch.int32).pin_memory()
+        self._mirror = not a.emulated and _env_flag("B200DP_HOST_MIRROR")
         self.master.copy_(init_flat(self.spec, seed, "cpu").to(self.device))
         K.cast_f32_to_bf16(self.master, self.w16)
         self._sharded_ranges: List[Tuple[int, int]] = []
@@ -284,6 +311,7 @@ class B200Engine(Engine):
             self.comm_tail = [one(by["conv1."])]
             self.adasum = False
             self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
+            self._set_mirror(2)
             return
         self.comm_tail = []
         self.comm_dense = [rng(by["dense.kernel"])]
@@ -301,6 +329,15 @@ class B200Engine(Engine):
         self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1."]), rng(by["conv2."])]
         self.adasum = adasum
         self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
+        self._set_mirror(0 if adasum else 1)
+
+    def _set_mirror(self, channel: int) -> None:
+        """Name the channel whose fused kernel ends the step: it also stores the step's loss/correct slot to the host ring."""
+        if not self._mirror:
+            return
+        K.check(K.lib().b200_comm_set_step_mirror(self.arena.h, channel, self.seg_ctrl, CTRL_LOSS_RING, CTRL_CORRECT_RING, RING,
+                                                  ctypes.c_void_p(self.host_loss.data_ptr()),
+                                                  ctypes.c_void_p(self.host_correct.data_ptr())), "set_step_mirror")
 
     # ------------------------------------------------------------------------------------ kernels
     def _forward(self, B: int, training: bool) -> None:
@@ -645,6 +682,9 @@ class B200Engine(Engine):
         self.global_step += 1
         self._shards_stale = bool(self._sharded_ranges)
         slot = self.global_step % RING
+        if self._mirror:
+            ev = self._buf_free[par]
+            return StepResult(_HostScalar(self.host_loss, slot, ev), _HostScalar(self.host_correct, slot, ev), B)
         return StepResult(_LazyScalar(self._ring_read(slot, True)), _LazyScalar(self._ring_read(slot, False)), B)
 
     def _ring_read(self, slot: int, loss: bool) -> torch.Tensor:

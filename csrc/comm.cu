@@ -54,6 +54,14 @@ struct Comm {
   unsigned long long timeout_cycles = 40ull * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
   uint32_t skew_ns = 0;
   void* emu_args = nullptr;   // device scratch for per-rank argument blocks (emulated only)
+  // Step-result mirror (b200_comm_set_step_mirror): the fused kernel of `mirror_channel` — the last kernel of a training
+  // step — copies that step's loss / correct-count ring slot into pinned host memory, so the host reads a step's result
+  // without a device-to-host copy operation in the stream between two steps.
+  int mirror_channel = -1, mirror_ring = 0;
+  const float* mirror_loss = nullptr;
+  const int* mirror_correct = nullptr;
+  float* mirror_host_loss = nullptr;
+  int* mirror_host_correct = nullptr;
 };
 
 struct PadPtrs {
@@ -114,6 +122,11 @@ struct FusedArgs {
   int nranges;
   Range ranges[B200_MAX_RANGES];
   unsigned long long timeout;
+  const float* mir_loss;      // step-result mirror (all null when unused): device rings -> mapped pinned host rings
+  const int* mir_correct;
+  float* mir_host_loss;
+  int* mir_host_correct;
+  int mir_ring;
 };
 
 struct AdamCoef {
@@ -252,6 +265,13 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
     rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
   }
   if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+  if (a.mir_host_loss != nullptr && bid == 0 && threadIdx.x == 0) {
+    // the head kernel finished this step's slot long ago (stream order); posted stores over PCIe, visible to the host
+    // once this kernel has completed
+    const int slot = (int)((uint32_t)*a.step_ptr % (uint32_t)a.mir_ring);
+    a.mir_host_loss[slot] = a.mir_loss[slot];
+    a.mir_host_correct[slot] = a.mir_correct[slot];
+  }
 }
 
 // -------------------------------------------------------------------------------------------
@@ -575,6 +595,23 @@ int b200_comm_rank(b200_comm_t h) { return ((Comm*)h)->rank; }
 int b200_comm_nranks(b200_comm_t h) { return ((Comm*)h)->n; }
 int b200_comm_is_emulated(b200_comm_t h) { return ((Comm*)h)->emulated ? 1 : 0; }
 
+// loss/correct rings at (ctrl_seg, loss_off / correct_off), `ring` slots each; host_loss/host_correct: pinned host memory
+// the device can address (cudaHostAlloc / torch pin_memory under UVA), `ring` slots each.  channel < 0 switches it off.
+int b200_comm_set_step_mirror(b200_comm_t h, int channel, int ctrl_seg, size_t loss_off, size_t correct_off, int ring,
+                              float* host_loss, int* host_correct) {
+  Comm* c = (Comm*)h;
+  if (channel < 0) { c->mirror_channel = -1; return B200_OK; }
+  B200_REQUIRE(channel < MAXCH && ring > 0 && host_loss && host_correct, "set_step_mirror: bad arguments");
+  B200_REQUIRE(ctrl_seg >= 0 && ctrl_seg < (int)c->segs.size() && loss_off + (size_t)ring * 4 <= c->segs[ctrl_seg].bytes &&
+                   correct_off + (size_t)ring * 4 <= c->segs[ctrl_seg].bytes, "set_step_mirror: rings outside segment %d", ctrl_seg);
+  const int me = c->emulated ? 0 : c->rank;
+  c->mirror_loss = (const float*)((char*)c->segs[ctrl_seg].base[me] + loss_off);
+  c->mirror_correct = (const int*)((char*)c->segs[ctrl_seg].base[me] + correct_off);
+  c->mirror_host_loss = host_loss; c->mirror_host_correct = host_correct; c->mirror_ring = ring;
+  c->mirror_channel = channel;
+  return B200_OK;
+}
+
 int b200_comm_set_timeout_ms(b200_comm_t h, double ms) {
   Comm* c = (Comm*)h;
   int khz = 0;
@@ -708,6 +745,10 @@ int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthre
     a.nranges = nranges;
     for (int i = 0; i < nranges; ++i) a.ranges[i] = Range{range_start[i], range_numel[i], range_algo[i], range_zero_other[i]};
     a.timeout = c->timeout_cycles;
+    if (channel == c->mirror_channel && !c->emulated) {
+      a.mir_loss = c->mirror_loss; a.mir_correct = c->mirror_correct;
+      a.mir_host_loss = c->mirror_host_loss; a.mir_host_correct = c->mirror_host_correct; a.mir_ring = c->mirror_ring;
+    }
   }
   if (nthreads <= 256)
     return launch_ranked(c, args, fused_allreduce_adam_kernel<false, true>, fused_allreduce_adam_kernel<true, true>, nblocks, nthreads,
@@ -1011,6 +1052,12 @@ extern "C" int b200_adasum_pair_static(const float* a, const float* b, float* ou
   int rc = static_scratch_for_current_device(&p.partials);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  // A call is two kernels that hand the partial sums to each other through the shared scratch.  Host threads calling
+  // into ONE stream must not interleave them (dots A, dots B, combine A would combine with B's sums), so the pair is
+  // enqueued under a lock; the stream then keeps whole calls in order.  Calls on different streams can still overlap on
+  // the GPU — that remains the caller's to avoid.
+  static std::mutex launch_mu;
+  std::lock_guard<std::mutex> lk(launch_mu);
   adasum_pair_dots_kernel<<<nblocks, 256, 0, st>>>(p);
   B200_LAUNCH_CHECK();
   adasum_pair_combine_kernel<<<nblocks * 2, 256, 0, st>>>(p, nblocks);

@@ -32,6 +32,11 @@ int b200_comm_rank(b200_comm_t h);
 int b200_comm_nranks(b200_comm_t h);
 int b200_comm_is_emulated(b200_comm_t h);
 int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
+/* The fused kernel launched on `channel` (the last kernel of a training step) also copies that step's slot of the
+ * loss / correct-count rings into pinned host memory: the per-step result the reference prints
+ * (horovod/tensorflow_mnist.py:148-149) reaches the host without a copy operation between two steps. */
+int b200_comm_set_step_mirror(b200_comm_t h, int channel, int ctrl_seg, size_t loss_off, size_t correct_off, int ring,
+                              float* host_loss, int* host_correct);
 int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns);   /* race hunting: random delay before each barrier arrival */
 int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out /* 64 B or NULL */);
 int b200_comm_seg_open(b200_comm_t h, int seg_id, const void* all_handles /* nranks x 64 B */);
@@ -89,7 +94,8 @@ int b200_adasum_level(b200_comm_t h, int channel, int nblocks, int level, int cu
  * b200_adasum_level — for callers that may not allocate device memory: it needs no communicator and calls no
  * cudaMalloc/cudaFree; its scratch is a 48 KiB array built into the library (resident on every GPU that loads
  * it, until exit).  Limits: nblocks <= B200_ADASUM_STATIC_MAX_BLOCKS, nseg <= B200_MAX_SEGMENTS; larger requests
- * fail with an error.  All calls on a device share that scratch: run them on one stream, never overlapping.
+ * fail with an error.  All calls on a device share that scratch: run them on one stream, never overlapping (several
+ * host threads may call into that one stream: the two kernels of a call are enqueued together under a lock).
  * The first call on each device resolves the scratch address (cudaGetSymbolAddress) — make it before any stream
  * capture starts. */
 int b200_adasum_pair_static(const float* a, const float* b, float* out, int nblocks, int nseg,

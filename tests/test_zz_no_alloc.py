@@ -92,3 +92,76 @@ def test_static_scratch_variant_rejects_oversize_requests():
     assert b"at most 32 tensor segments" in lib.b200_last_error()
     assert fn(None, x.data_ptr(), x.data_ptr(), 8, 1, one, cnt, stream) != 0
     torch.cuda.synchronize()
+
+
+def _pair_on(fn, lib, dev, seed, sizes, nblocks=8):
+    """One call on `dev` (made current, as the entry point requires); returns (out, xa, xb, starts)."""
+    starts = [sum(sizes[:i]) for i in range(len(sizes))]
+    n = sum(sizes)
+    st, sz = (LL * len(sizes))(*starts), (LL * len(sizes))(*sizes)
+    with torch.cuda.device(dev):
+        g = torch.Generator(device="cpu").manual_seed(seed)
+        xa = torch.randn(n, generator=g).to(f"cuda:{dev}")
+        xb = (torch.randn(n, generator=g) * 0.5).to(f"cuda:{dev}") + 0.1 * xa
+        out = torch.empty(n, device=f"cuda:{dev}")
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        rc = fn(xa.data_ptr(), xb.data_ptr(), out.data_ptr(), nblocks, len(sizes), st, sz, stream)
+        assert rc == 0, lib.b200_last_error().decode()
+        torch.cuda.synchronize()
+    return out, xa, xb, starts
+
+
+@pytest.mark.multigpu(2)
+def test_static_scratch_is_resolved_per_device():
+    """Every GPU that loads the library carries its own copy of the scratch array, and the entry point looks its address
+    up separately for each device: a call made with device 1 current must use device 1's array (device 0's address
+    would fault there or land in the wrong memory).  Calls alternate between the two devices, twice each."""
+    lib, fn = _cabi()
+    sizes = [4096, 32, 1000]
+    for rnd in range(2):
+        for dev in (1, 0):
+            out, xa, xb, starts = _pair_on(fn, lib, dev, 100 + 10 * rnd + dev, sizes)
+            tree = torch.cat([adasum_tree([xa[s:s + l].cpu(), xb[s:s + l].cpu()]) for s, l in zip(starts, sizes)])
+            assert torch.allclose(out.cpu(), tree, rtol=1e-4, atol=1e-5), (rnd, dev)
+
+
+def test_static_scratch_calls_from_two_host_threads_on_one_stream():
+    """Two host threads of one process may both call the entry point as long as their calls do not overlap on the GPU:
+    here both launch into the SAME stream, which serialises the kernels, while the host-side set-up (the per-device
+    address cache) is hit concurrently."""
+    import threading
+    lib, fn = _cabi()
+    sizes = [2048, 64, 7000]
+    starts = [sum(sizes[:i]) for i in range(len(sizes))]
+    n = sum(sizes)
+    st, sz = (LL * len(sizes))(*starts), (LL * len(sizes))(*sizes)
+    dev = torch.cuda.current_device()
+    s = torch.cuda.Stream()
+    per_thread, errs = 6, []
+    ins = [[(torch.randn(n, device="cuda"), torch.randn(n, device="cuda")) for _ in range(per_thread)] for _ in range(2)]
+    outs = [[torch.empty(n, device="cuda") for _ in range(per_thread)] for _ in range(2)]
+    torch.cuda.synchronize()
+
+    def work(t):
+        try:
+            torch.cuda.set_device(dev)
+            for k in range(per_thread):
+                xa, xb = ins[t][k]
+                rc = fn(xa.data_ptr(), xb.data_ptr(), outs[t][k].data_ptr(), 8, len(sizes), st, sz, ctypes.c_void_p(s.cuda_stream))
+                if rc != 0:
+                    errs.append(lib.b200_last_error().decode())
+        except Exception as e:                      # noqa: BLE001
+            errs.append(repr(e))
+
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(2)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    s.synchronize()
+    assert not errs, errs
+    for t in range(2):
+        for k in range(per_thread):
+            xa, xb = ins[t][k]
+            tree = torch.cat([adasum_tree([xa[a:a + l].cpu(), xb[a:a + l].cpu()]) for a, l in zip(starts, sizes)])
+            assert torch.allclose(outs[t][k].cpu(), tree, rtol=1e-4, atol=1e-5), (t, k)
