@@ -175,6 +175,46 @@ class CheckpointManager:
             return self.save(state_fn(), step)
         return None
 
+    # -- asynchronous saves ---------------------------------------------------
+    def save_async(self, pending, step: int) -> None:
+        """``pending``: a handle whose ``result()`` returns the state dict (``B200Engine.state_async``).  The file is
+        written by a background thread — the training thread does not wait for the device-to-host drain, the
+        serialisation or the fsync.  One save is in flight at a time; ``wait()`` joins it."""
+        if not self.enabled:
+            return
+        self.wait()
+        self._last_save_t = time.monotonic()
+        self._last_save_step = int(step)
+
+        def run():
+            try:
+                self._async_path = self.save(pending.result(), step)
+            except Exception as e:          # surfaced by wait()
+                self._async_err = e
+        import threading
+        self._async_err = None
+        self._writer = threading.Thread(target=run, name="b200dp-ckpt-writer", daemon=False)
+        self._writer.start()
+
+    def wait(self) -> Optional[str]:
+        """Join the save in flight (if any); re-raises its error."""
+        w = getattr(self, "_writer", None)
+        if w is not None:
+            w.join()
+            self._writer = None
+            err = getattr(self, "_async_err", None)
+            if err is not None:
+                self._async_err = None
+                raise err
+            return getattr(self, "_async_path", None)
+        return None
+
+    def maybe_save_async(self, pending_fn, step: int) -> bool:
+        if self.due(step):
+            self.save_async(pending_fn(), step)
+            return True
+        return False
+
 
 def export_model(directory: str, tensors: Dict[str, torch.Tensor], meta: Dict[str, Any]) -> str:
     """Final inference export (reference: ``model.save('./final_model')``):

@@ -89,6 +89,18 @@ class _HostScalar:
         return self._get()
 
 
+class _PendingState:
+    """Handle of an asynchronous state snapshot (B200Engine.state_async)."""
+
+    def __init__(self, host: torch.Tensor, event: torch.cuda.Event, T: int, meta: Dict[str, Any]):
+        self.host, self.event, self.T, self.meta = host, event, T, meta
+
+    def result(self) -> Dict[str, Any]:
+        self.event.synchronize()
+        T, h = self.T, self.host
+        return {"tensors": {"params": h[:T], "adam_m": h[T:2 * T], "adam_v": h[2 * T:3 * T]}, "meta": self.meta}
+
+
 def _env_flag(name: str, default: str = "1") -> bool:
     return os.environ.get(name, default) not in ("0", "false", "no")
 
@@ -185,6 +197,12 @@ class B200Engine(Engine):
         self.host_loss = torch.zeros(RING, dtype=torch.float32).pin_memory()
         self.host_correct = torch.zeros(RING, dtype=torch.int32).pin_memory()
         self._mirror = not a.emulated and _env_flag("B200DP_HOST_MIRROR")
+        # B200DP_POISON=1 (race hunting): whatever the protocol says nobody reads any more is overwritten with
+        # NaN — consumed gradient buffers by the fused kernels, the activations the peers gather by a fill after the
+        # step's last barrier — so a late reader turns the loss into NaN instead of training on stale or zero data
+        self.poison = _env_flag("B200DP_POISON", "0")
+        if self.poison:
+            a.set_debug_poison(True)
         self.master.copy_(init_flat(self.spec, seed, "cpu").to(self.device))
         K.cast_f32_to_bf16(self.master, self.w16)
         self._sharded_ranges: List[Tuple[int, int]] = []
@@ -547,6 +565,9 @@ class B200Engine(Engine):
         # every peer reaches this kernel's barrier after its own weight pushes: passing it means the new dense weights of
         # ALL owners have landed here, and that nobody still reads this rank's a2/dz
         self._timed(self._comm, 2, self.comm_tail, par, nblocks=1, nthreads=256)
+        if self.poison:
+            self.a2.fill_(float("nan"))      # every peer has passed the barrier above: nobody may gather these any more
+            self.dz.fill_(float("nan"))
 
     def _comm(self, channel: int, ranges, par: int, *, reduce: Optional[bool] = None, grad_off: Optional[int] = None,
               scale: Optional[float] = None, nblocks: Optional[int] = None, nthreads: int = 512) -> None:
@@ -587,6 +608,8 @@ class B200Engine(Engine):
         nvtx = self._nvtx
         if nvtx:
             torch.cuda.nvtx.range_push("b200dp.forward")
+        if self.poison:
+            self.grads[par].zero_()          # the fused kernels left NaN here instead of zeros
         self._forward(B, True)
         self._head(B, True)
         if nvtx:
@@ -739,12 +762,14 @@ class B200Engine(Engine):
         return torch.cat(outs)
 
     # ------------------------------------------------------------------------------------ state
-    def _gather_sharded(self) -> None:
-        """One-sided: pull every owner's slice of the two-shot ranges into the local fp32 state.
-        Safe between steps: peers cannot start their next update before this rank joins its barrier."""
+    def _gather_sharded(self, sync: bool = True) -> None:
+        """One-sided: pull every owner's slice of the sharded ranges into the local fp32 state (copies in stream order).
+        Safe between steps: this rank's step has passed its last barrier, so every owner's update is complete, and no
+        peer can start its next update before this rank — whose stream runs these copies first — joins the next barrier."""
         if self.n == 1 or not self._sharded_ranges or not self._shards_stale:
             return
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         T = self.T
         for (st, ln) in self._sharded_ranges:
             chunk = (-(-ln // self.n) + 3) // 4 * 4
@@ -756,7 +781,8 @@ class B200Engine(Engine):
                     continue
                 for base in (0, T, 2 * T):
                     self.arena.pull_from_peer(self.seg_state, (base + st + lo) * 4, (hi - lo) * 4, r)
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         self._shards_stale = False
 
     def finalize(self) -> None:
@@ -782,6 +808,38 @@ class B200Engine(Engine):
             meta["optimizer"] = dict(lr=a.lr, beta1=a.beta1, beta2=a.beta2, epsilon=a.epsilon, eps_mode=a.eps_mode)
         return {"tensors": {"params": self.master.cpu().clone(), "adam_m": self.m.cpu().clone(), "adam_v": self.v.cpu().clone()},
                 "meta": meta}
+
+    def state_async(self) -> "_PendingState":
+        """Checkpoint without stalling the job: the fp32 state is snapshotted device-to-device in stream order (~12 us for
+        the MNIST CNN), training continues at once, and the snapshot drains to pinned host memory on the copy stream.
+        ``result()`` of the returned handle (called by the checkpoint writer thread) waits for that copy only.  Peers
+        therefore never sit in a device-side barrier while rank 0 writes a file."""
+        self._gather_sharded(sync=False)
+        T = self.T
+        if getattr(self, "_snap", None) is None:
+            self._snap = torch.empty(3 * T, device=self.device, dtype=torch.float32)
+            self._snap_host = [torch.empty(3 * T, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._snap_ev = [torch.cuda.Event() for _ in range(2)]
+            self._snap_i = 0
+            self.ckpt_stream = torch.cuda.Stream(device=self.device)      # not the input-copy stream: a 40 MB drain would delay batches
+        i = self._snap_i
+        self._snap_i ^= 1
+        self._snap_ev[i].synchronize()                       # the writer that used this host buffer two saves ago is long done
+        main = torch.cuda.current_stream()
+        main.wait_stream(self.ckpt_stream)                   # an earlier drain must not still be reading the snapshot
+        self._snap.copy_(self.arena.view(self.seg_state, 0, 3 * T, torch.float32), non_blocking=True)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        self.ckpt_stream.wait_event(ready)
+        with torch.cuda.stream(self.ckpt_stream):
+            self._snap_host[i].copy_(self._snap, non_blocking=True)
+            self._snap_ev[i].record(self.ckpt_stream)
+        meta = self.meta()
+        meta.update(global_step=self.global_step, seed=self.seed, engine="b200")
+        if self.adam is not None:
+            a = self.adam
+            meta["optimizer"] = dict(lr=a.lr, beta1=a.beta1, beta2=a.beta2, epsilon=a.epsilon, eps_mode=a.eps_mode)
+        return _PendingState(self._snap_host[i], self._snap_ev[i], T, meta)
 
     def load_state(self, tensors: Dict[str, torch.Tensor], meta: Dict[str, Any]) -> None:
         if meta.get("arch", self.spec.arch) != self.spec.arch or tensors["params"].numel() != self.T:

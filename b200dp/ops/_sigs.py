@@ -21,6 +21,7 @@ _SIGS = {
     "b200_comm_set_timeout_ms": (I, [P, D]),
     "b200_comm_set_step_mirror": (I, [P, I, I, SZ, SZ, I, P, P]),
     "b200_comm_set_debug_skew_ns": (I, [P, C.c_uint]),
+    "b200_comm_set_debug_poison": (I, [P, I]),
     "b200_comm_seg_alloc": (I, [P, SZ, PI, P]),
     "b200_comm_seg_open": (I, [P, I, P]),
     "b200_comm_seg_ptr": (P, [P, I, I]),

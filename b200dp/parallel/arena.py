@@ -80,6 +80,10 @@ class SymmetricArena:
         """Race hunting: every barrier arrival is delayed by a pseudo-random time below ``max_ns``."""
         K.check(K.lib().b200_comm_set_debug_skew_ns(self.h, int(max_ns)), "set_debug_skew")
 
+    def set_debug_poison(self, on: bool) -> None:
+        """Race hunting: the fused kernels fill a gradient buffer they have consumed with NaN instead of zeros."""
+        K.check(K.lib().b200_comm_set_debug_poison(self.h, int(bool(on))), "set_debug_poison")
+
     def alloc(self, nbytes: int) -> int:
         """Collective: every rank must call with the same size, in the same order."""
         nbytes = _round_up(int(nbytes), 256)

@@ -123,13 +123,21 @@ class CheckpointSaverHook(SessionRunHook):
             session.metrics.checkpoints.inc()
 
     def after_run(self, session, result):
-        p = self.manager.maybe_save(session.engine.state, session.engine.global_step)
+        eng = session.engine
+        if hasattr(eng, "state_async"):
+            # periodic saves do not stall the job: device-side snapshot now, drain + file write on a background thread
+            if self.manager.maybe_save_async(eng.state_async, eng.global_step):
+                get_logger().info("checkpoint_started", step=eng.global_step)
+                self._count(session)
+            return
+        p = self.manager.maybe_save(eng.state, eng.global_step)
         if p:
-            get_logger().info("checkpoint_saved", path=p, step=session.engine.global_step)
+            get_logger().info("checkpoint_saved", path=p, step=eng.global_step)
             self._count(session)
 
     def end(self, session):
         if self.manager.enabled:
+            self.manager.wait()
             p = self.manager.save(session.engine.state(), session.engine.global_step)
             get_logger().info("checkpoint_saved", path=p, step=session.engine.global_step, final=True)
             self._count(session)

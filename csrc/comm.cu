@@ -53,6 +53,7 @@ struct Comm {
   std::vector<Seg> segs;
   unsigned long long timeout_cycles = 40ull * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
   uint32_t skew_ns = 0;
+  int poison = 0;             // debug: consumed gradient buffers are filled with NaN instead of zeros (b200_comm_set_debug_poison)
   void* emu_args = nullptr;   // device scratch for per-rank argument blocks (emulated only)
   // Step-result mirror (b200_comm_set_step_mirror): the fused kernel of `mirror_channel` — the last kernel of a training
   // step — copies that step's loss / correct-count ring slot into pinned host memory, so the host reads a step's result
@@ -127,6 +128,7 @@ struct FusedArgs {
   float* mir_host_loss;
   int* mir_host_correct;
   int mir_ring;
+  int poison;                 // debug: "clear the other-parity buffer" writes NaN (the engine zeroes it again before use)
 };
 
 struct AdamCoef {
@@ -212,6 +214,10 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
   if (multi) rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
   else __syncthreads();
   const AdamCoef c = coef;
+  // After the barrier above every peer has finished reading the other-parity buffer, so it may be cleared for the next
+  // accumulation.  Poison mode writes NaN instead: a reader that is late after all (a protocol bug) then poisons its
+  // weights and the loss instead of quietly summing zeros; the engine zeroes the buffer itself before it is used again.
+  const float clr = a.poison ? __int_as_float(0x7fc00000) : 0.f;
 
   bool any_twoshot = false;
   for (int ri = 0; ri < a.nranges; ++ri) {
@@ -228,7 +234,7 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
         adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
         st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
         *reinterpret_cast<uint2*>(a.w16[a.rank] + i) = pack_bf16x4(p);
-        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(0.f, 0.f, 0.f, 0.f));
+        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(clr, clr, clr, clr));
       }
     } else {
       // two-shot: reduce + update the owned slice, push the bf16 result to every rank
@@ -257,7 +263,7 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
       }
       if (rg.zero_other)
         for (long long q = tid; q < rg.numel / 4; q += nthr)
-          st_f4(a.grad_other + rg.start + q * 4, make_float4(0.f, 0.f, 0.f, 0.f));
+          st_f4(a.grad_other + rg.start + q * 4, make_float4(clr, clr, clr, clr));
     }
   }
   if (any_twoshot) {
@@ -620,6 +626,12 @@ int b200_comm_set_timeout_ms(b200_comm_t h, double ms) {
   return B200_OK;
 }
 
+// Debug aid: gradient buffers a fused kernel has consumed are filled with NaN instead of zeros.
+int b200_comm_set_debug_poison(b200_comm_t h, int on) {
+  ((Comm*)h)->poison = on ? 1 : 0;
+  return B200_OK;
+}
+
 // Debug aid: every barrier arrival is preceded by a pseudo-random sleep below max_ns nanoseconds.
 int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns) {
   ((Comm*)h)->skew_ns = max_ns;
@@ -745,6 +757,7 @@ int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthre
     a.nranges = nranges;
     for (int i = 0; i < nranges; ++i) a.ranges[i] = Range{range_start[i], range_numel[i], range_algo[i], range_zero_other[i]};
     a.timeout = c->timeout_cycles;
+    a.poison = c->poison;
     if (channel == c->mirror_channel && !c->emulated) {
       a.mir_loss = c->mirror_loss; a.mir_correct = c->mirror_correct;
       a.mir_host_loss = c->mirror_host_loss; a.mir_host_correct = c->mirror_host_correct; a.mir_ring = c->mirror_ring;

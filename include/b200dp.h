@@ -38,6 +38,7 @@ int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
 int b200_comm_set_step_mirror(b200_comm_t h, int channel, int ctrl_seg, size_t loss_off, size_t correct_off, int ring,
                               float* host_loss, int* host_correct);
 int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns);   /* race hunting: random delay before each barrier arrival */
+int b200_comm_set_debug_poison(b200_comm_t h, int on);             /* race hunting: consumed gradient buffers get NaN, not zeros */
 int b200_comm_seg_alloc(b200_comm_t h, size_t bytes, int* seg_id, void* ipc_handle_out /* 64 B or NULL */);
 int b200_comm_seg_open(b200_comm_t h, int seg_id, const void* all_handles /* nranks x 64 B */);
 void* b200_comm_seg_ptr(b200_comm_t h, int seg_id, int peer);

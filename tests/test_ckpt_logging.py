@@ -180,3 +180,39 @@ def test_restore_skips_a_damaged_newest_checkpoint(tmp_path, capsys):
             f.truncate(8)
     with pytest.raises(RuntimeError, match="no readable checkpoint"):
         CheckpointManager(str(tmp_path)).restore()
+
+
+def test_async_save_runs_on_a_writer_thread_and_surfaces_errors(tmp_path):
+    """CheckpointManager.save_async: the caller hands over a pending-state handle and returns at once; the file appears
+    after wait(); an error in the writer is re-raised by wait(), not lost."""
+    import threading
+    import time
+    import torch
+    from b200dp.ckpt.manager import CheckpointManager
+
+    gate = threading.Event()
+
+    class Pending:
+        def result(self):
+            gate.wait(10)
+            return {"tensors": {"params": torch.arange(8, dtype=torch.float32)}, "meta": {"arch": "x"}}
+
+    m = CheckpointManager(str(tmp_path), save_steps=5, save_secs=None)
+    t0 = time.monotonic()
+    assert m.maybe_save_async(Pending, 5) is True
+    assert time.monotonic() - t0 < 1.0 and m.latest() is None          # returned without waiting for the state
+    assert m.maybe_save_async(Pending, 5) is False                    # same step is not saved twice
+    gate.set()
+    path = m.wait()
+    assert path and m.latest() == path
+    r = m.restore()
+    assert torch.equal(r["tensors"]["params"], torch.arange(8, dtype=torch.float32)) and r["meta"]["step"] == 5
+
+    class Broken:
+        def result(self):
+            raise RuntimeError("device lost")
+
+    m.save_async(Broken(), 10)
+    import pytest
+    with pytest.raises(RuntimeError, match="device lost"):
+        m.wait()

@@ -179,3 +179,39 @@ def test_set_lr_takes_effect_without_graph_recapture(data):
     g.train_step(x[:B], y[:B])
     torch.cuda.synchronize()
     assert not torch.equal(g.master, before) and g._graphs == graphs and g.state()["meta"]["optimizer"]["lr"] == 1e-3
+
+
+def test_poison_mode_changes_nothing_when_the_protocol_holds(data, monkeypatch):
+    """B200DP_POISON=1 overwrites consumed gradient buffers and gathered activations with NaN (SURVEY §5.2 debug build).
+    A correct step never reads them again, so the run must track the normal one (up to the order of the fp32 atomics in
+    the split-K and weight-gradient reductions, which differs from run to run)."""
+    x, y, _, _ = data
+    B = 64
+    a, _ = _pair(B, True, use_graph=True)
+    monkeypatch.setenv("B200DP_POISON", "1")
+    b, _ = _pair(B, True, use_graph=True)
+    assert b.poison and not a.poison
+    for s in range(8):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        la, lb = a.train_step(xb, yb).loss_value(), b.train_step(xb, yb).loss_value()
+        assert np.isfinite(lb) and abs(la - lb) < 2e-3 * max(1.0, abs(la)), (s, la, lb)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(b.master).all())
+    assert (a.w16.float() - b.w16.float()).abs().max().item() < 4e-3
+
+
+def test_state_async_snapshot_equals_state_and_is_not_disturbed_by_later_steps(data):
+    x, y, _, _ = data
+    B = 64
+    g, _ = _pair(B, True, use_graph=True)
+    for s in range(4):
+        g.train_step(x[s * B:(s + 1) * B], y[s * B:(s + 1) * B])
+    want = g.state()
+    pend = g.state_async()
+    for s in range(4, 8):                       # training goes on while the snapshot drains
+        g.train_step(x[s * B:(s + 1) * B], y[s * B:(s + 1) * B])
+    got = pend.result()
+    for k in ("params", "adam_m", "adam_v"):
+        assert torch.equal(got["tensors"][k], want["tensors"][k]), k
+    assert got["meta"]["global_step"] == 4
+    assert not torch.equal(g.state()["tensors"]["params"], want["tensors"]["params"])

@@ -38,6 +38,9 @@ def _check(res, np_, algo):
     r0 = res[0]
     assert r0["ckpt_step"] == 6
     algo = algo.split("@")[0]
+    if algo.endswith("+poison"):
+        algo = algo[:-len("+poison")]
+        assert r0["poison"]
     if algo != "adasum":
         assert r0["oracle_cos"] > 0.9 and r0["adam_m_cos"] > 0.95, r0
     if algo in ("twoshot", "gemm_rs"):
@@ -53,7 +56,7 @@ def _check(res, np_, algo):
 
 
 @pytest.mark.multigpu(2)
-@pytest.mark.parametrize("algo", ["auto", "oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
+@pytest.mark.parametrize("algo", ["auto", "auto+poison", "twoshot+poison", "oneshot", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_two_gpus(tmp_path, algo):
     _check(_run(2, algo, tmp_path), 2, algo)
 
@@ -74,6 +77,6 @@ def test_four_gpus(tmp_path, algo):
 
 
 @pytest.mark.multigpu(8)
-@pytest.mark.parametrize("algo", ["auto", "twoshot", "adasum", "nvls", "gemm_rs"])
+@pytest.mark.parametrize("algo", ["auto", "auto+poison", "twoshot", "adasum", "nvls", "gemm_rs"])
 def test_eight_gpus(tmp_path, algo):
     _check(_run(8, algo, tmp_path), 8, algo)

@@ -18,6 +18,9 @@ if "@" in algo:                             # "<algo>@<arch>", e.g. gemm_rs@kera
     algo, arch = algo.split("@")
 if algo == "nvls":                         # also route large public broadcasts through the switch (multimem.st)
     os.environ["B200DP_BCAST"] = "nvls"
+if algo.endswith("+poison"):               # consumed buffers are overwritten with NaN: a late reader poisons the loss
+    os.environ["B200DP_POISON"] = "1"
+    algo = algo[:-len("+poison")]
 if algo == "gemm_rs":                      # two-shot with the dense wgrad GEMM fused with its reduce-scatter
     os.environ["B200DP_GEMM_RS"] = "1"
     algo = "twoshot"
@@ -79,6 +82,7 @@ res["engine_nvls"] = bool(eng.nvls)
 res["nvls_bcast_used"] = bool(getattr(hvd.world().arena, "_staging_mc", False))
 res["gemm_rs"] = bool(eng.gemm_rs)
 res["dense_fused"] = bool(eng.dense_fused)
+res["poison"] = bool(eng.poison)
 res["algos"] = [r[2] for r in eng.comm_dense + eng.comm_rest]
 
 # rank 0 alone takes a checkpoint (one-sided gather of sharded Adam state) while the others wait at a barrier

@@ -54,6 +54,18 @@ if e.dense_fused:
     ops["fused_adam(conv2,out,dense.bias)"] = lambda: e._comm(1, e.comm_rest, 0, nblocks=64, nthreads=256)
     ops["fused_adam(conv1: step tail)"] = lambda: e._comm(2, e.comm_tail, 0, nblocks=1, nthreads=256)
     del ops["dense_wgrad(tc)"]
+    # the same kernel in the shape one of 8 ranks runs: K = 8*B gathered rows, M = F/8 owned rows (no peers to store to here)
+    Fs8 = e.F // 8
+    A8 = torch.randn(8 * B, Fs8, device="cuda").to(torch.bfloat16)
+    B8 = (torch.randn(8 * B, e.D, device="cuda") * 0.01).to(torch.bfloat16)
+    dk = e.spec.param("dense.kernel")
+    for bn in (64, 128):
+        if e.D % bn:
+            continue
+        ops[f"dense_wgrad+adam as 1 of 8 owners (K=8B, bn={bn})"] = (lambda bn=bn: K.gemm_tc_wgrad_adam(
+            e.arena.h, A8, B8, Fs8, e.D, 8 * B, Fs8, e.D, state_seg=e.seg_state, master_off=0, m_off=T4, v_off=2 * T4,
+            w16_seg=e.seg_w16, w16_off=0, ctrl_seg=e.seg_ctrl, step_off=0, hyper_off=16, param_start=dk.offset, row0=0,
+            gscale=0.125, block_n=bn))
 else:
     ops["fused_adam(dense bucket)"] = lambda: e._comm(0, e.comm_dense, 0)
     ops["fused_adam(rest)"] = lambda: e._comm(1, e.comm_rest, 0)
