@@ -41,6 +41,7 @@ from .spec import ModelSpec, get_spec, init_flat
 bf16 = torch.bfloat16
 RING = 1024
 CTRL_STEP, CTRL_HYPER, CTRL_EVAL_LOSS, CTRL_EVAL_CORRECT, CTRL_LOSS_RING, CTRL_CORRECT_RING = 0, 16, 64, 80, 256, 256 + RING * 4
+CTRL_POW, CTRL_COEF = 96, 128          # beta1^t / beta2^t (2 doubles); this step's Adam coefficients (5 floats)
 CTRL_BYTES = 256 + RING * 8
 
 
@@ -188,6 +189,12 @@ class B200Engine(Engine):
         self.w16 = a.view(self.seg_w16, 0, T, bf16)
         self.step_dev = a.view(self.seg_ctrl, CTRL_STEP, 1, torch.int32)
         self.hyper_dev = a.view(self.seg_ctrl, CTRL_HYPER, 5, torch.float64)
+        self.pow_dev = a.view(self.seg_ctrl, CTRL_POW, 2, torch.float64)
+        # the first kernel of a step multiplies the beta powers once and leaves the step's Adam coefficients in the control
+        # block; the optimizer kernels read them instead of running two fp64 pow() each
+        self._coef_cache = not a.emulated and _env_flag("B200DP_COEF_CACHE")
+        if self._coef_cache:
+            K.check(K.lib().b200_comm_set_coef_cache(a.h, self.seg_ctrl, CTRL_COEF), "set_coef_cache")
         self.eval_loss = a.view(self.seg_ctrl, CTRL_EVAL_LOSS, 1, torch.float32)
         self.eval_correct = a.view(self.seg_ctrl, CTRL_EVAL_CORRECT, 1, torch.int32)
         self.loss_ring = a.view(self.seg_ctrl, CTRL_LOSS_RING, RING, torch.float32)
@@ -286,8 +293,16 @@ class B200Engine(Engine):
             a = self.adam
             self.hyper_dev.copy_(torch.tensor([a.lr, a.beta1, a.beta2, a.epsilon, 0.0 if a.eps_mode == "tf" else 1.0],
                                               dtype=torch.float64))
+            self._set_step_dev()
         self._graphs.clear()
         self._plan_comm()
+
+    def _set_step_dev(self) -> None:
+        """Device step counter and the beta-power accumulators that go with it (beta^step, like TensorFlow's beta1_power /
+        beta2_power variables): written whenever the step or the betas change outside the kernels."""
+        self.step_dev.fill_(self.global_step)
+        b1, b2 = (self.adam.beta1, self.adam.beta2) if self.adam is not None else (0.9, 0.999)
+        self.pow_dev.copy_(torch.tensor([b1 ** self.global_step, b2 ** self.global_step], dtype=torch.float64))
 
     def set_lr(self, lr: float) -> None:
         """The kernels read the learning rate from device memory at run time, so a new value needs no graph re-capture."""
@@ -327,6 +342,19 @@ class B200Engine(Engine):
             one = lambda b: (b.start, b.numel, 0, 1)
             self.comm_rest = [one(by["conv2."]), one(by["dense.bias+out."])]
             self.comm_tail = [one(by["conv1."])]
+            if self.reduce and _env_flag("B200DP_MERGE_TAIL"):
+                # across ranks ONE kernel reduces all small tensors at the end of the step: its barrier is the step's
+                # closing barrier anyway, and the peers' 250 KB arrive by bulk copies in a single NVLink round trip, so a
+                # second collective (with a barrier of its own, contending with the dense update) buys nothing
+                self.comm_tail = [one(by["conv1."]), one(by["conv2."]), one(by["dense.bias+out."])]
+                self.comm_rest = []
+                if _env_flag("B200DP_PUSH_TAIL"):
+                    # ... and the ranks do not fetch each other's slices after the barrier: each stores its own into the
+                    # peers' inboxes in front of its flag (one one-way latency instead of two round trips)
+                    bpp = (self.n * sum(r[1] for r in self.comm_tail) * 4 + 255) // 256 * 256
+                    if getattr(self, "seg_inbox", None) is None or self._inbox_bpp < bpp:
+                        self.seg_inbox, self._inbox_bpp = self.arena.alloc(2 * bpp), bpp
+                    K.check(K.lib().b200_comm_set_inbox(self.arena.h, 2, self.seg_inbox, self._inbox_bpp), "set_inbox")
             self.adasum = False
             self.scale = 1.0 / self.n if (self.reduce and self.dist.op is C.Average) else 1.0
             self._set_mirror(2)
@@ -364,10 +392,10 @@ class B200Engine(Engine):
         ring = dict(loss_ring=self.loss_ring if training else None, correct_ring=self.correct_ring if training else None)
         if self.keras:
             K.conv1_valid_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1,
-                              self.step_dev if training else None, bump_step=training, **ring)
+                              self.step_dev if training else None, bump_step=(2 if self._coef_cache else 1) if training else 0, **ring)
         else:
             K.conv1_pool_fwd(x, self.pv("conv1.kernel", w), self.pv("conv1.bias", w), a1, self.am1[:B],
-                             self.step_dev if training else None, bump_step=training, **ring)
+                             self.step_dev if training else None, bump_step=(2 if self._coef_cache else 1) if training else 0, **ring)
         k2, b2 = self.pv("conv2.kernel", w), self.pv("conv2.bias", w)
         if self.tc_conv:
             K.conv_tc_fwd(a1, k2, b2, a2, am2, relu=True, pool=True, pad=self.PAD2)
@@ -551,9 +579,9 @@ class B200Engine(Engine):
         ev_dg2.record(main)
         with torch.cuda.stream(s2):
             s2.wait_event(ev_hw)
-            s2.wait_event(ev_dg2)        # the update rewrites the conv2 weights the dgrad above is reading
-            # one 16-byte column per thread: the kernel is a barrier plus ONE round of peer loads, not a loop of them
-            self._timed(self._comm, 1, self.comm_rest, par, nblocks=64, nthreads=256)
+            if self.comm_rest:
+                s2.wait_event(ev_dg2)        # the update rewrites the conv2 weights the dgrad above is reading
+                self._timed(self._comm, 1, self.comm_rest, par, nblocks=64, nthreads=256)
             ev_s2 = torch.cuda.Event()
             ev_s2.record(s2)
         if self.keras:
@@ -564,7 +592,7 @@ class B200Engine(Engine):
         main.wait_event(ev_s1)
         # every peer reaches this kernel's barrier after its own weight pushes: passing it means the new dense weights of
         # ALL owners have landed here, and that nobody still reads this rank's a2/dz
-        self._timed(self._comm, 2, self.comm_tail, par, nblocks=1, nthreads=256)
+        self._timed(self._comm, 2, self.comm_tail, par, nblocks=1 if len(self.comm_tail) == 1 else 64, nthreads=256)
         if self.poison:
             self.a2.fill_(float("nan"))      # every peer has passed the barrier above: nobody may gather these any more
             self.dz.fill_(float("nan"))
@@ -850,7 +878,7 @@ class B200Engine(Engine):
             self.v.copy_(tensors["adam_v"].to(self.device))
         K.cast_f32_to_bf16(self.master, self.w16)
         self.global_step = int(meta.get("global_step", meta.get("step", 0)))
-        self.step_dev.fill_(self.global_step)
+        self._set_step_dev()
         if "seed" in meta:
             self.seed = int(meta["seed"])
             self._graphs.clear()
@@ -873,7 +901,7 @@ class B200Engine(Engine):
         if seed != self.seed or (step & 1) != (self.global_step & 1):
             self._graphs.clear()
         self.global_step, self.seed = step, seed
-        self.step_dev.fill_(self.global_step)
+        self._set_step_dev()
         self._shards_stale = False
         torch.cuda.synchronize()
         _w.barrier()

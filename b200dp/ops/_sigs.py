@@ -20,6 +20,8 @@ _SIGS = {
     "b200_comm_is_emulated": (I, [P]),
     "b200_comm_set_timeout_ms": (I, [P, D]),
     "b200_comm_set_step_mirror": (I, [P, I, I, SZ, SZ, I, P, P]),
+    "b200_comm_set_inbox": (I, [P, I, I, SZ]),
+    "b200_comm_set_coef_cache": (I, [P, I, SZ]),
     "b200_comm_set_debug_skew_ns": (I, [P, C.c_uint]),
     "b200_comm_set_debug_poison": (I, [P, I]),
     "b200_comm_seg_alloc": (I, [P, SZ, PI, P]),

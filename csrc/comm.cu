@@ -20,6 +20,7 @@
 // B200 (ranks that wait on one another must never be separate launches on one GPU).
 #include <cooperative_groups.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -28,6 +29,7 @@
 
 #include "../include/b200dp.h"
 #include "common.cuh"
+#include "tc_sm100.cuh"
 
 namespace {
 
@@ -58,6 +60,12 @@ struct Comm {
   // Step-result mirror (b200_comm_set_step_mirror): the fused kernel of `mirror_channel` — the last kernel of a training
   // step — copies that step's loss / correct-count ring slot into pinned host memory, so the host reads a step's result
   // without a device-to-host copy operation in the stream between two steps.
+  // Push inbox (b200_comm_set_inbox): one-shot launches on `inbox_channel` do not pull the peers' gradients after a
+  // barrier (two NVLink round trips) — every rank stores its slice into each peer's inbox and then raises the flag, so
+  // the data rides in front of the flag and the wait costs one one-way latency.
+  const float* coef_cache[MAXR] = {};   // per rank (emulated communicators hold all of them); null: kernels compute the coefficients
+  int inbox_channel = -1, inbox_seg = -1;
+  size_t inbox_bytes_per_parity = 0;
   int mirror_channel = -1, mirror_ring = 0;
   const float* mirror_loss = nullptr;
   const int* mirror_correct = nullptr;
@@ -69,6 +77,7 @@ struct PadPtrs {
   uint32_t* flags[MAXR];   // every rank's flag array (peer-mapped)
   uint32_t* epochs;        // this rank's epoch counters
   uint32_t skew_ns;        // debug: pseudo-random delay (< skew_ns) before every barrier arrival, to provoke races
+  uint32_t trace;          // debug (B200DP_COMM_TRACE=1): block 0 prints the phase times of every 256th launch
 };
 
 // -------------------------------------------------------------------------------------------
@@ -100,6 +109,15 @@ __device__ __forceinline__ void rank_barrier(const PadPtrs& pad, int channel, in
   __syncthreads();
 }
 
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tc::smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(tc::smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(tc::smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+
 struct Range {
   long long start;    // elements
   long long numel;    // multiple of 4
@@ -129,6 +147,11 @@ struct FusedArgs {
   int* mir_host_correct;
   int mir_ring;
   int poison;                 // debug: "clear the other-parity buffer" writes NaN (the engine zeroes it again before use)
+  const float* coef_cache;    // Adam coefficients of this step, precomputed by the step's first kernel (else null: computed here)
+  int bulk;                   // WIDE kernel, one-shot ranges only: peers' slices arrive by TMA bulk copies into shared memory
+  int push;                   // WIDE kernel, one-shot ranges only: slices are pushed into the peers' inboxes ahead of the flag
+  float* inbox[MAXR];         // every rank's inbox for this parity: [source rank][compact range index]
+  long long inbox_stride;     // floats per source rank (sum of the range lengths)
 };
 
 struct AdamCoef {
@@ -196,7 +219,10 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
   const bool multi = a.n > 1 && a.reduce;
 
   __shared__ AdamCoef coef;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && a.coef_cache != nullptr) {
+    coef.b1 = a.coef_cache[0]; coef.b2 = a.coef_cache[1]; coef.eps = a.coef_cache[2];
+    coef.step_size = a.coef_cache[3]; coef.vscale = a.coef_cache[4];
+  } else if (threadIdx.x == 0) {
     const int t = *a.step_ptr;
     const double lr = a.hyper[0], b1 = a.hyper[1], b2 = a.hyper[2], eps = a.hyper[3];
     const double bc1 = 1.0 - pow(b1, (double)t), bc2 = 1.0 - pow(b2, (double)t);
@@ -211,6 +237,83 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
       coef.vscale = (float)(1.0 / sqrt(bc2));
     }
   }
+  if (WIDE && a.push && multi) {
+    // ---- push-based one-shot ------------------------------------------------------------------------------------
+    // 1. store this rank's slice of every range into each peer's inbox (row = this rank), 2. fence + flag exchange
+    // (the barrier doubles as "data has arrived"), 3. sum own gradient + the N-1 inbox rows in rank order, Adam.
+    const int me = a.rank;
+    const bool tr = a.pad.trace && bid == 0 && threadIdx.x == 0 && (epoch & 255u) == 0;
+    unsigned long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    if (tr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    long long cbase = 0;
+    for (int ri = 0; ri < a.nranges; ++ri) {
+      const Range rg = a.ranges[ri];
+      const long long nq = rg.numel / 4, per = (nq + gridDim.x - 1) / gridDim.x;
+      const long long q0 = min(nq, (long long)bid * per), q1 = min(nq, q0 + per);
+      for (long long q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
+        const float4 g = ld_f4(a.grad[me] + rg.start + q * 4);
+        // the fp32 state of these parameters was last touched a whole step ago (150 MB of traffic since): start
+        // bringing it into L2 now, underneath the flag exchange
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.master + rg.start + q * 4));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.m + rg.start + q * 4));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.v + rg.start + q * 4));
+        float* dst = nullptr;
+#pragma unroll 1
+        for (int r = 0; r < a.n; ++r)
+          if (r != me) { dst = a.inbox[r] + (long long)me * a.inbox_stride + cbase + q * 4; st_f4(dst, g); }
+      }
+      cbase += rg.numel;
+    }
+    if (tr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    // no per-thread fence: the barrier's __syncthreads orders every thread's inbox stores before the flag threads, and
+    // their st.release.sys is cumulative over everything that happened before it
+    rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+    if (tr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2));
+    const AdamCoef c = coef;
+    const float clr = a.poison ? __int_as_float(0x7fc00000) : 0.f;
+    cbase = 0;
+    for (int ri = 0; ri < a.nranges; ++ri) {
+      const Range rg = a.ranges[ri];
+      const long long nq = rg.numel / 4, per = (nq + gridDim.x - 1) / gridDim.x;
+      const long long q0 = min(nq, (long long)bid * per), q1 = min(nq, q0 + per);
+      for (long long q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
+        const long long i = rg.start + q * 4;
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        float4 t[MAXR];
+#pragma unroll
+        for (int r = 0; r < MAXR; ++r)
+          if (r < a.n) t[r] = r == me ? ld_f4(a.grad[me] + i) : ld_f4(a.inbox[me] + (long long)r * a.inbox_stride + cbase + q * 4);
+        float4 g = t[0];
+#pragma unroll
+        for (int r = 1; r < MAXR; ++r)
+          if (r < a.n) { g.x += t[r].x; g.y += t[r].y; g.z += t[r].z; g.w += t[r].w; }
+        g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        *reinterpret_cast<uint2*>(a.w16[me] + i) = pack_bf16x4(p);
+        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(clr, clr, clr, clr));
+      }
+      cbase += rg.numel;
+    }
+    if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+    if (a.mir_host_loss != nullptr && bid == 0 && threadIdx.x == 0) {
+      const int slot = (int)((uint32_t)*a.step_ptr % (uint32_t)a.mir_ring);
+      a.mir_host_loss[slot] = a.mir_loss[slot];
+      a.mir_host_correct[slot] = a.mir_correct[slot];
+    }
+    if (tr) {
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t3));
+      printf("b200dp trace: rank %d ch %d epoch %u: push %llu ns, barrier %llu ns, reduce+adam %llu ns\n", a.rank, a.channel, epoch,
+             t1 - t0, t2 - t1, t3 - t2);
+    }
+    return;
+  }
+  if (WIDE && a.bulk && multi && threadIdx.x == 0) {
+    extern __shared__ __align__(128) uint8_t fsm0[];
+    tc::mbar_init(reinterpret_cast<uint64_t*>(fsm0), 1);
+    tc::fence_barrier_init();
+  }
   if (multi) rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
   else __syncthreads();
   const AdamCoef c = coef;
@@ -218,6 +321,71 @@ __global__ void __launch_bounds__(WIDE ? 256 : 512, 2) fused_allreduce_adam_kern
   // accumulation.  Poison mode writes NaN instead: a reader that is late after all (a protocol bug) then poisons its
   // weights and the loss instead of quietly summing zeros; the engine zeroes the buffer itself before it is used again.
   const float clr = a.poison ? __int_as_float(0x7fc00000) : 0.f;
+
+  if (WIDE && a.bulk && multi) {
+    // One-shot over the copy engine: every block owns a contiguous run of 16-byte columns of each range; one thread
+    // pulls that run from all N ranks into shared memory with TMA bulk copies (one NVLink round trip for everything,
+    // no long-latency loads parked in the SM's load queue in front of a co-resident kernel's), then the block sums
+    // the N copies in rank order and applies Adam.
+    extern __shared__ __align__(128) uint8_t fsm[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(fsm);
+    float4* buf = reinterpret_cast<float4*>(fsm + 128);
+    // (the barrier was initialised before the rank barrier, see below)
+    if (threadIdx.x == 0) {
+      uint32_t total = 0;
+      for (int ri = 0; ri < a.nranges; ++ri) {
+        const long long nq = a.ranges[ri].numel / 4, per = (nq + gridDim.x - 1) / gridDim.x;
+        const long long q0 = min(nq, (long long)bid * per), q1 = min(nq, q0 + per);
+        total += (uint32_t)((q1 - q0) * 16 * a.n);
+      }
+      if (total) {
+        tc::mbar_arrive_expect_tx(bar, total);
+        float4* dst = buf;
+        for (int ri = 0; ri < a.nranges; ++ri) {
+          const long long nq = a.ranges[ri].numel / 4, per = (nq + gridDim.x - 1) / gridDim.x;
+          const long long q0 = min(nq, (long long)bid * per), q1 = min(nq, q0 + per);
+          if (q1 > q0)
+            for (int r = 0; r < a.n; ++r) {
+              bulk_g2s(dst, a.grad[r] + a.ranges[ri].start + q0 * 4, (uint32_t)((q1 - q0) * 16), bar);
+              dst += q1 - q0;
+            }
+        }
+      } else {
+        tc::mbar_arrive(bar);
+      }
+    }
+    tc::mbar_wait(bar, 0, 41);
+    const float4* src = buf;
+    for (int ri = 0; ri < a.nranges; ++ri) {
+      const Range rg = a.ranges[ri];
+      const long long nq = rg.numel / 4, per = (nq + gridDim.x - 1) / gridDim.x;
+      const long long q0 = min(nq, (long long)bid * per), q1 = min(nq, q0 + per);
+      const int cnt = (int)(q1 - q0);
+      for (int j = threadIdx.x; j < cnt; j += blockDim.x) {
+        const long long i = rg.start + (q0 + j) * 4;
+        float4 p = ld_f4(a.master + i), m = ld_f4(a.m + i), v = ld_f4(a.v + i);
+        float4 g = src[j];
+        for (int r = 1; r < a.n; ++r) {
+          const float4 t = src[(size_t)r * cnt + j];
+          g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+        g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+        adam_elem(g.x, p.x, m.x, v.x, c); adam_elem(g.y, p.y, m.y, v.y, c);
+        adam_elem(g.z, p.z, m.z, v.z, c); adam_elem(g.w, p.w, m.w, v.w, c);
+        st_f4(a.master + i, p); st_f4(a.m + i, m); st_f4(a.v + i, v);
+        *reinterpret_cast<uint2*>(a.w16[a.rank] + i) = pack_bf16x4(p);
+        if (rg.zero_other) st_f4(a.grad_other + i, make_float4(clr, clr, clr, clr));
+      }
+      src += (size_t)a.n * cnt;
+    }
+    if (threadIdx.x == 0) a.pad.epochs[a.channel * MAXB + bid] = epoch;
+    if (a.mir_host_loss != nullptr && bid == 0 && threadIdx.x == 0) {
+      const int slot = (int)((uint32_t)*a.step_ptr % (uint32_t)a.mir_ring);
+      a.mir_host_loss[slot] = a.mir_loss[slot];
+      a.mir_host_correct[slot] = a.mir_correct[slot];
+    }
+    return;
+  }
 
   bool any_twoshot = false;
   for (int ri = 0; ri < a.nranges; ++ri) {
@@ -451,6 +619,86 @@ __global__ void __launch_bounds__(128, 8) allgather_acts_kernel(const GatherArgs
   }
 }
 
+// The same gather on the copy engine of the SM (TMA bulk copies, no multicast): one thread per block moves 16 KB pieces
+// peer -> shared memory -> local memory through a ring of four slots with mbarrier completion.  Why not plain loads: a
+// peer load stays ~3 us in the SM's load queue, and the loads of whatever convolution CTA shares that SM queue up
+// behind it (measured: the conv2 dgrad beside the load-based gather went from 14 to 29 us).  Bulk copies bypass that
+// queue, and the 64 KB ring makes the blocks settle on the SMs the 128-CTA convolution grids leave free.
+constexpr int GSLOT = 16384, GSLOTS = 4;
+
+template <bool EMU>
+__global__ void __launch_bounds__(32) allgather_acts_bulk_kernel(const GatherArgs areal, const GatherArgs* aemu) {
+  extern __shared__ __align__(128) uint8_t gsm[];
+  const GatherArgs& a = EMU ? aemu[blockIdx.y] : areal;
+  const int bid = blockIdx.x;
+  uint32_t epoch = a.pad.epochs[a.channel * MAXB + bid];
+  rank_barrier(a.pad, a.channel, bid, a.rank, a.n, ++epoch, a.timeout);
+  if (threadIdx.x != 0) return;
+  a.pad.epochs[a.channel * MAXB + bid] = epoch;
+  uint64_t* full = reinterpret_cast<uint64_t*>(gsm + GSLOTS * GSLOT);
+  for (int s = 0; s < GSLOTS; ++s) tc::mbar_init(full + s, 1);
+  tc::fence_barrier_init();
+  const int Fs = a.F / a.n;
+  const int row_b = Fs * 2;                                   // bytes of one row of the owned slice (multiple of 16)
+  const long long dz_b = (long long)a.B * a.D * 2;            // bytes of one rank's dz (multiple of 16)
+  const int n_dz = (int)((dz_b + GSLOT - 1) / GSLOT);
+  const int rg = row_b <= GSLOT ? GSLOT / row_b : 0;          // rows per piece; 0: a row is split into column segments
+  const int segs = rg ? 1 : (row_b + GSLOT - 1) / GSLOT;
+  const int n_act = rg ? (a.B + rg - 1) / rg : a.B * segs;
+  const int per_peer = n_dz + n_act;
+  const int total = per_peer * a.n;
+  const int cnt = bid < total ? (total - bid + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  // piece k of this block -> loads into slot k % GSLOTS; returns the bytes and where they go
+  auto issue = [&](int k, bf16** dst_out, uint32_t* bytes_out, bool do_load) {
+    const int i = bid + k * (int)gridDim.x;
+    const int pr = i / per_peer, j = i - pr * per_peer;
+    const int p = (pr + a.rank) % a.n;                        // own rank first, then the peers in ring order
+    uint8_t* slot = gsm + (k % GSLOTS) * GSLOT;
+    uint64_t* bar = full + (k % GSLOTS);
+    if (j < n_dz) {
+      const long long off = (long long)j * GSLOT;
+      const uint32_t bytes = (uint32_t)min((long long)GSLOT, dz_b - off);
+      if (do_load) { tc::mbar_arrive_expect_tx(bar, bytes); bulk_g2s(slot, (const uint8_t*)a.dz[p] + off, bytes, bar); }
+      *dst_out = reinterpret_cast<bf16*>((uint8_t*)a.dz_out + (size_t)p * dz_b + off);
+      *bytes_out = bytes;
+    } else if (rg) {
+      const int b0 = (j - n_dz) * rg, nb = min(rg, a.B - b0);
+      if (do_load) {
+        tc::mbar_arrive_expect_tx(bar, (uint32_t)(nb * row_b));
+        for (int r = 0; r < nb; ++r)
+          bulk_g2s(slot + r * row_b, a.act[p] + (size_t)(b0 + r) * a.F + (size_t)a.rank * Fs, (uint32_t)row_b, bar);
+      }
+      *dst_out = a.act_out + ((size_t)p * a.B + b0) * Fs;
+      *bytes_out = (uint32_t)(nb * row_b);
+    } else {
+      const int q = j - n_dz, b = q / segs, sg = q - b * segs;
+      const int c0 = sg * GSLOT;
+      const uint32_t bytes = (uint32_t)min(GSLOT, row_b - c0);
+      if (do_load) {
+        tc::mbar_arrive_expect_tx(bar, bytes);
+        bulk_g2s(slot, (const uint8_t*)(a.act[p] + (size_t)b * a.F + (size_t)a.rank * Fs) + c0, bytes, bar);
+      }
+      *dst_out = reinterpret_cast<bf16*>((uint8_t*)(a.act_out + ((size_t)p * a.B + b) * Fs) + c0);
+      *bytes_out = bytes;
+    }
+  };
+  bf16* dst;
+  uint32_t bytes;
+  for (int k = 0; k < min(cnt, GSLOTS); ++k) issue(k, &dst, &bytes, true);
+  for (int k = 0; k < cnt; ++k) {
+    tc::mbar_wait(full + (k % GSLOTS), (uint32_t)((k / GSLOTS) & 1), 40);
+    issue(k, &dst, &bytes, false);
+    bulk_s2g(dst, gsm + (k % GSLOTS) * GSLOT, bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    if (k + GSLOTS < cnt) {
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");     // the slot has been read out: refill it
+      issue(k + GSLOTS, &dst, &bytes, true);
+    }
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");              // all stores have landed before the grid completes
+}
+
 // -------------------------------------------------------------------------------------------
 // Adasum: log2(N) levels; at level L rank r pairs with r ^ (1<<L).
 //   a' = (1 - a.b/(2|a|^2)) a + (1 - a.b/(2|b|^2)) b      per tensor segment
@@ -545,6 +793,9 @@ void fill_pad(Comm* c, int as_rank, PadPtrs* p) {
   for (int r = 0; r < c->n; ++r) p->flags[r] = (uint32_t*)seg_ptr(c, 0, r, 0);
   p->epochs = (uint32_t*)seg_ptr(c, 0, as_rank, PAD_FLAGS_BYTES);
   p->skew_ns = c->skew_ns;
+  static int tr = -1;
+  if (tr < 0) { const char* e = getenv("B200DP_COMM_TRACE"); tr = (e && e[0] == '1') ? 1 : 0; }
+  p->trace = (uint32_t)tr;
 }
 
 template <typename Args, typename KReal, typename KEmu, typename... Extra>
@@ -565,6 +816,23 @@ int launch_ranked(Comm* c, Args* per_rank, KReal kreal, KEmu kemu, int nblocks, 
   return B200_OK;
 }
 
+template <typename Args, typename KReal, typename KEmu>
+int launch_ranked_smem(Comm* c, Args* per_rank, KReal kreal, KEmu kemu, int nblocks, int nthreads, size_t smem, cudaStream_t st) {
+  if (!c->emulated) {
+    kreal<<<nblocks, nthreads, smem, st>>>(per_rank[0], nullptr);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
+  B200_REQUIRE(sizeof(Args) * c->n <= 65536, "argument block too large");
+  B200_CHECK(cudaMemcpyAsync(c->emu_args, per_rank, sizeof(Args) * c->n, cudaMemcpyHostToDevice, st));
+  const Args* dev = (const Args*)c->emu_args;
+  Args dummy = per_rank[0];
+  void* params[] = {(void*)&dummy, (void*)&dev};
+  B200_CHECK(cudaLaunchCooperativeKernel((void*)kemu, dim3(nblocks, c->n), dim3(nthreads), params, smem, st));
+  B200_CHECK(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
 }  // namespace
 
 void b200_set_error(const char* fmt, ...) {
@@ -577,6 +845,11 @@ void b200_set_error(const char* fmt, ...) {
 }
 
 void b200_forget_mcsegs(void* comm);   // defined with the NVLS code below
+
+const float* b200_comm_coef_cache(b200_comm_t h, int rank) {
+  Comm* c = (Comm*)h;
+  return (rank >= 0 && rank < MAXR) ? c->coef_cache[rank] : nullptr;
+}
 
 extern "C" {
 
@@ -600,6 +873,29 @@ int b200_comm_create(int rank, int nranks, int emulated, b200_comm_t* out) {
 int b200_comm_rank(b200_comm_t h) { return ((Comm*)h)->rank; }
 int b200_comm_nranks(b200_comm_t h) { return ((Comm*)h)->n; }
 int b200_comm_is_emulated(b200_comm_t h) { return ((Comm*)h)->emulated ? 1 : 0; }
+
+// The fused kernels read the step's Adam coefficients (5 floats) from (ctrl_seg, off) instead of computing them; the
+// engine's first kernel of a step writes them (b200_conv1_pool_fwd with bump_step = 2).  ctrl_seg < 0 switches it off.
+int b200_comm_set_coef_cache(b200_comm_t h, int ctrl_seg, size_t off) {
+  Comm* c = (Comm*)h;
+  for (int r = 0; r < MAXR; ++r) c->coef_cache[r] = nullptr;
+  if (ctrl_seg < 0) return B200_OK;
+  B200_REQUIRE(ctrl_seg < (int)c->segs.size() && off + 20 <= c->segs[ctrl_seg].bytes && off % 4 == 0, "set_coef_cache: bad segment/offset");
+  for (int r = 0; r < c->n; ++r)
+    if (c->emulated || r == c->rank) c->coef_cache[r] = (const float*)((char*)c->segs[ctrl_seg].base[r] + off);
+  return B200_OK;
+}
+
+// seg: a symmetric segment of 2 * bytes_per_parity bytes (zero or garbage, it is only read after being written);
+// one-shot launches on `channel` whose ranges fit (nranks * sum(numel) * 4 <= bytes_per_parity) then push instead of pull.
+int b200_comm_set_inbox(b200_comm_t h, int channel, int seg, size_t bytes_per_parity) {
+  Comm* c = (Comm*)h;
+  if (channel < 0) { c->inbox_channel = -1; return B200_OK; }
+  B200_REQUIRE(channel < MAXCH && seg >= 0 && seg < (int)c->segs.size() && 2 * bytes_per_parity <= c->segs[seg].bytes &&
+                   bytes_per_parity % 16 == 0, "set_inbox: bad channel/segment/size");
+  c->inbox_channel = channel; c->inbox_seg = seg; c->inbox_bytes_per_parity = bytes_per_parity;
+  return B200_OK;
+}
 
 // loss/correct rings at (ctrl_seg, loss_off / correct_off), `ring` slots each; host_loss/host_correct: pinned host memory
 // the device can address (cudaHostAlloc / torch pin_memory under UVA), `ring` slots each.  channel < 0 switches it off.
@@ -758,14 +1054,55 @@ int b200_fused_allreduce_adam(b200_comm_t h, int channel, int nblocks, int nthre
     for (int i = 0; i < nranges; ++i) a.ranges[i] = Range{range_start[i], range_numel[i], range_algo[i], range_zero_other[i]};
     a.timeout = c->timeout_cycles;
     a.poison = c->poison;
+    a.coef_cache = c->coef_cache[me];
     if (channel == c->mirror_channel && !c->emulated) {
       a.mir_loss = c->mirror_loss; a.mir_correct = c->mirror_correct;
       a.mir_host_loss = c->mirror_host_loss; a.mir_host_correct = c->mirror_host_correct; a.mir_ring = c->mirror_ring;
     }
   }
-  if (nthreads <= 256)
-    return launch_ranked(c, args, fused_allreduce_adam_kernel<false, true>, fused_allreduce_adam_kernel<true, true>, nblocks, nthreads,
-                         (cudaStream_t)stream);
+  if (nthreads <= 256) {
+    // small buckets: TMA bulk prefetch of the peers' slices when every range is one-shot and the slices fit shared memory
+    static int bulk_ok = -1;
+    if (bulk_ok < 0) {
+      const char* e = getenv("B200DP_ONESHOT_BULK");
+      bulk_ok = (e && e[0] == '0') ? 0 : 1;
+      if (bulk_ok) {
+        B200_CHECK(cudaFuncSetAttribute(fused_allreduce_adam_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        B200_CHECK(cudaFuncSetAttribute(fused_allreduce_adam_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      }
+    }
+    size_t smem = 0;
+    bool bulk = bulk_ok && reduce && c->n > 1;
+    for (int i = 0; i < nranges && bulk; ++i) {
+      if (range_algo[i] != 0) bulk = false;
+      smem += (size_t)((range_numel[i] / 4 + nblocks - 1) / nblocks) * 16 * c->n;
+    }
+    if (bulk && smem + 128 > 160 * 1024) bulk = false;
+    // push inbox registered for this channel: data travels in front of the flag (one one-way latency)
+    bool push = false;
+    if (channel == c->inbox_channel && reduce && c->n > 1) {
+      long long ctot = 0;
+      push = true;
+      for (int i = 0; i < nranges; ++i) {
+        if (range_algo[i] != 0) push = false;
+        ctot += range_numel[i];
+      }
+      if ((size_t)ctot * 4 * c->n > c->inbox_bytes_per_parity) push = false;
+      if (push) {
+        const size_t poff = grad_cur_off > grad_other_off ? c->inbox_bytes_per_parity : 0;
+        for (int k = 0; k < nr; ++k) {
+          args[k].push = 1;
+          args[k].inbox_stride = ctot;
+          for (int r = 0; r < c->n; ++r) args[k].inbox[r] = (float*)seg_ptr(c, c->inbox_seg, r, poff);
+        }
+        bulk = false;
+      }
+    }
+    smem = bulk ? smem + 128 : 0;
+    for (int k = 0; k < nr; ++k) args[k].bulk = bulk ? 1 : 0;
+    return launch_ranked_smem(c, args, fused_allreduce_adam_kernel<false, true>, fused_allreduce_adam_kernel<true, true>, nblocks,
+                              nthreads, smem, (cudaStream_t)stream);
+  }
   return launch_ranked(c, args, fused_allreduce_adam_kernel<false, false>, fused_allreduce_adam_kernel<true, false>, nblocks, nthreads,
                        (cudaStream_t)stream);
 }
@@ -871,7 +1208,20 @@ int b200_allgather_acts(b200_comm_t h, int channel, int nblocks, int act_seg, si
     a.B = B; a.F = F; a.D = D;
     a.timeout = c->timeout_cycles;
   }
-  return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 128, (cudaStream_t)stream);
+  static int bulk = -1;
+  if (bulk < 0) {
+    const char* e = getenv("B200DP_GATHER_BULK");
+    bulk = (e && e[0] == '0') ? 0 : 1;
+    if (bulk) {
+      const size_t sm = (size_t)GSLOTS * GSLOT + 64;
+      B200_CHECK(cudaFuncSetAttribute(allgather_acts_bulk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      B200_CHECK(cudaFuncSetAttribute(allgather_acts_bulk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    }
+  }
+  if (!bulk)
+    return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 128, (cudaStream_t)stream);
+  return launch_ranked_smem(c, args, allgather_acts_bulk_kernel<false>, allgather_acts_bulk_kernel<true>, nblocks < 40 ? nblocks : 40, 32,
+                            (size_t)GSLOTS * GSLOT + 64, (cudaStream_t)stream);
 }
 
 size_t b200_adasum_scratch_bytes(int nblocks, int nseg) { return (size_t)nblocks * nseg * 3 * sizeof(double); }

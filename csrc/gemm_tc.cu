@@ -13,6 +13,8 @@
 #include "../include/b200dp.h"
 #include "tc_sm100.cuh"
 
+const float* b200_comm_coef_cache(b200_comm_t h, int rank);   // comm.cu
+
 namespace tc {
 
 EncodeTiledFn get_encode_tiled() {
@@ -84,6 +86,13 @@ struct GemmParams {
   const int* step_ptr;
   const double* hyper;   // lr, beta1, beta2, eps, eps_mode (0: TF placement, 1: torch placement)
   float gscale;
+  int tma_push;          // 1: the bf16 tile leaves through ONE TMA tensor store per destination rank (needs 16-byte aligned rows)
+  const float* coef;     // this step's Adam coefficients (5 floats) when the engine caches them; else computed from step/hyper
+};
+
+// out_mode 4: one tensor map per destination rank over the bf16 rows this rank owns (stores clip at the slice's end)
+struct TmapPack {
+  CUtensorMap m[B200_MAX_RANKS];
 };
 
 struct AdamCoefG {
@@ -103,7 +112,8 @@ __device__ __forceinline__ void adam1(float g, float& p, float& m, float& v, con
 }
 
 __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                         const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+                                                         const __grid_constant__ CUtensorMap tmB,
+                                                         const __grid_constant__ TmapPack tmW, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int stage_bytes = A_TILE_BYTES + p.bn * BK * 2;
@@ -239,7 +249,10 @@ __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__
       // pipeline stages are free by then (every MMA has retired), so the tile reuses them: row pitch bn floats, 16-byte
       // columns XOR-swizzled with the row so that this row-per-thread store and the coalesced sweep below are both
       // conflict-free.  Part 2 (all six warps) follows the role branches.
-      if (warp == 2 && lane == 0) {
+      if (warp == 2 && lane == 0 && p.coef != nullptr) {
+        AdamCoefG* co = reinterpret_cast<AdamCoefG*>(smem + NSTAGE * stage_bytes + 128);
+        co->b1 = p.coef[0]; co->b2 = p.coef[1]; co->eps = p.coef[2]; co->step_size = p.coef[3]; co->vscale = p.coef[4];
+      } else if (warp == 2 && lane == 0) {
         AdamCoefG* co = reinterpret_cast<AdamCoefG*>(smem + NSTAGE * stage_bytes + 128);
         const int t = *p.step_ptr;
         const double lr = p.hyper[0], b1 = p.hyper[1], b2 = p.hyper[2], eps = p.hyper[3];
@@ -320,6 +333,7 @@ __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__
     __syncthreads();
     const AdamCoefG co = *reinterpret_cast<const AdamCoefG*>(smem + NSTAGE * stage_bytes + 128);
     const float* tile = reinterpret_cast<const float*>(smem);
+    bf16* wt = reinterpret_cast<bf16*>(smem + NSTAGE * stage_bytes + 256);     // [128][bn] bf16, row-major: the TMA store's source
     const int bn = p.bn, f4_per_row = bn >> 2, total = BM * f4_per_row;
     const int nr = p.nranks;
     const float gs = p.gscale;
@@ -348,11 +362,32 @@ __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__
         adam1(g.z * gs, pp[u].z, mm[u].z, vv[u].z, co); adam1(g.w * gs, pp[u].w, mm[u].w, vv[u].w, co);
         st_f4(p.master + idx[u], pp[u]); st_f4(p.adam_m + idx[u], mm[u]); st_f4(p.adam_v + idx[u], vv[u]);
         const uint2 w = pack_bf16x4(pp[u]);
+        if (p.tma_push) {
+          *reinterpret_cast<uint2*>(wt + (size_t)rl * bn + c4 * 4) = w;
+        } else {
 #pragma unroll 1
-        for (int r = 0; r < nr; ++r) *reinterpret_cast<uint2*>(p.w16[r] + idx[u]) = w;
+          for (int r = 0; r < nr; ++r) *reinterpret_cast<uint2*>(p.w16[r] + idx[u]) = w;
+        }
       }
     }
-    if (nr > 1) __threadfence_system();   // weights pushed into the peers are visible before this grid completes
+    if (p.tma_push) {
+      // The refreshed bf16 tile goes to every rank (this one included) as ONE TMA tensor store each: the copy engine
+      // streams the 128 rows over NVLink while the SM is already done.  Per-thread 8-byte stores to 8 peers held this
+      // kernel at 27-29 us on 2 and 8 GPUs (10-12 us of it is the sweep): remote stores back up in the store queue.
+      fence_proxy_async();                 // generic-proxy writes of the tile -> visible to the async proxy
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        for (int r = 0; r < nr; ++r)
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmW.m[r]), "r"(n0), "r"(m0),
+                       "r"(smem_u32(wt))
+                       : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");     // stores performed before the grid completes
+        if (nr > 1) __threadfence_system();
+      }
+    } else if (nr > 1) {
+      __threadfence_system();   // weights pushed into the peers are visible before this grid completes
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -369,11 +404,12 @@ struct AdamEpilogue {
   const int* step_ptr;
   const double* hyper;
   float gscale;
+  const float* coef;
 };
 
 static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* peerC, int rows_per_owner, int M, int N, int K, int lda,
                           int ldb, int ldc, int a_mn_major, int b_mn_major, int out_mode, int split_k, int block_n, void* stream,
-                          const AdamEpilogue* adam = nullptr) {
+                          const AdamEpilogue* adam = nullptr, const TmapPack* wmaps = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: bad shape %dx%dx%d", M, N, K);
   B200_REQUIRE(out_mode >= 0 && out_mode <= 4, "gemm_tc: out_mode %d", out_mode);
   B200_REQUIRE((out_mode == 4) == (adam != nullptr), "gemm_tc: out_mode 4 needs the Adam epilogue arguments");
@@ -415,6 +451,8 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
     for (int r = 0; r < B200_MAX_RANKS; ++r) p.w16[r] = adam->w16[r];
     p.nranks = adam->nranks; p.param_base = adam->param_base; p.step_ptr = adam->step_ptr; p.hyper = adam->hyper;
     p.gscale = adam->gscale;
+    p.tma_push = wmaps ? 1 : 0;
+    p.coef = adam->coef;
   }
   p.C = C; p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.a_mn = a_mn_major; p.b_mn = b_mn_major; p.out_mode = out_mode; p.bn = block_n;
@@ -438,7 +476,7 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
     p.bulk_rs = (out_mode == 3 && !(e && e[0] == '0')) ? 1 : 0;
   }
   const size_t smem = (size_t)p.nstage * (A_TILE_BYTES + block_n * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/ +
-                      (p.bulk_rs ? 128 * 64 * sizeof(float) : 0);
+                      (p.bulk_rs ? 128 * 64 * sizeof(float) : 0) + (p.tma_push ? (size_t)BM * block_n * 2 : 0);
   static size_t smem_set = 0;
   if (smem > smem_set) {
     B200_CHECK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -446,7 +484,8 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
   }
   B200_REQUIRE(smem <= 200 * 1024, "gemm_tc: %zu bytes of shared memory needed", smem);
   dim3 grid((N + block_n - 1) / block_n, (M + BM - 1) / BM, split_k);
-  B200_CHECK(launch_pdl(gemm_tc_kernel, grid, dim3(192), smem, (cudaStream_t)stream, tmA, tmB, p));
+  static const TmapPack no_maps = {};
+  B200_CHECK(launch_pdl(gemm_tc_kernel, grid, dim3(192), smem, (cudaStream_t)stream, tmA, tmB, wmaps ? *wmaps : no_maps, p));
   return B200_OK;
 }
 
@@ -509,5 +548,23 @@ extern "C" int b200_gemm_tc_wgrad_adam(b200_comm_t comm, const void* A, const vo
   ep.step_ptr = (const int*)(ct + step_off);
   ep.hyper = (const double*)(ct + hyper_off);
   ep.gscale = gscale;
-  return gemm_tc_launch(A, B, ep.master, nullptr, 0, M, N, K, lda, ldb, N, 1, 1, 4, 1, block_n, stream, &ep);
+  ep.coef = b200_comm_coef_cache(comm, as_rank);
+  // TMA tensor stores need 16-byte aligned rows: parameter index of the slice's first element a multiple of 8, N too
+  static int tma_ok = -1;
+  if (tma_ok < 0) {
+    const char* e = getenv("B200DP_TMA_PUSH");
+    tma_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  TmapPack maps;
+  const bool push = tma_ok && nranks > 1 && ep.param_base % 8 == 0 && N % 8 == 0;   // alone, direct stores are 1.3 us faster
+  if (push) {
+    memset(&maps, 0, sizeof maps);
+    for (int r = 0; r < nranks; ++r) {
+      const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 2};
+      const uint32_t box[2] = {(uint32_t)block_n, 128};
+      int rc = tc::make_tmap_bf16(&maps.m[r], ep.w16[r] + ep.param_base, 2, dims, str, box, 0);
+      if (rc) return rc;
+    }
+  }
+  return gemm_tc_launch(A, B, ep.master, nullptr, 0, M, N, K, lda, ldb, N, 1, 1, 4, 1, block_n, stream, &ep, push ? &maps : nullptr);
 }

@@ -13,6 +13,24 @@ __device__ __forceinline__ float bf(const bf16* p) { return __bfloat162float(*p)
 // conv1: 5x5 SAME, Cin=1 -> C1, + bias + ReLU + 2x2 maxpool, one image per block.
 // Lane = output channel (weights live in registers), input tile + halo in shared memory.
 // ------------------------------------------------------------------------------------------------
+// bump_step == 2: the control block the step counter lives in follows the engine's layout — hyper-parameters (lr, beta1,
+// beta2, eps, eps_mode as doubles) at +16 bytes, the running powers beta1^t / beta2^t (doubles, TensorFlow's beta-power
+// accumulators, horovod/tensorflow_mnist.py:130) at +96, and the Adam coefficients of THIS step (5 floats: beta1, beta2, eps,
+// step size, v scale) at +128.  Updating the powers by one multiplication here, once per step, takes the two fp64 pow()
+// calls out of every optimizer kernel's prologue (2-3 us of a single thread in front of each of them).
+__device__ __forceinline__ void adam_coef_update(int* step_ptr) {
+  const double* hyper = reinterpret_cast<const double*>(reinterpret_cast<char*>(step_ptr) + 16);
+  double* pw = reinterpret_cast<double*>(reinterpret_cast<char*>(step_ptr) + 96);
+  float* cf = reinterpret_cast<float*>(reinterpret_cast<char*>(step_ptr) + 128);
+  const double lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3];
+  const double b1p = pw[0] * b1, b2p = pw[1] * b2;
+  pw[0] = b1p; pw[1] = b2p;
+  const double bc1 = 1.0 - b1p, bc2 = 1.0 - b2p;
+  cf[0] = (float)b1; cf[1] = (float)b2; cf[2] = (float)eps;
+  if (hyper[4] == 0.0) { cf[3] = (float)(lr * sqrt(bc2) / bc1); cf[4] = 1.f; }
+  else { cf[3] = (float)(lr / bc1); cf[4] = (float)(1.0 / sqrt(bc2)); }
+}
+
 __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __restrict__ x, const bf16* __restrict__ w,
                                                              const bf16* __restrict__ bias, bf16* __restrict__ out,
                                                              uint8_t* __restrict__ argmax, int C1, int* step_ptr,
@@ -25,6 +43,7 @@ __global__ void __launch_bounds__(256) conv1_pool_fwd_kernel(const float* __rest
     const int s = *step_ptr + 1;          // the step that starts now
     *step_ptr = s;
     if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+    if (bump_step == 2) adam_coef_update(step_ptr);
   }
   for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) {
     const int r = i >> 5, c = i & 31;
@@ -156,6 +175,7 @@ __global__ void __launch_bounds__(256) conv1_valid_fwd_kernel(const float* __res
     const int s = *step_ptr + 1;
     *step_ptr = s;
     if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+    if (bump_step == 2) adam_coef_update(step_ptr);
   }
   for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
   __syncthreads();
@@ -270,6 +290,7 @@ __global__ void __launch_bounds__(256) conv1_valid3_fwd_v8_kernel(const float* _
     const int s = *step_ptr + 1;
     *step_ptr = s;
     if (ring > 0) { loss_ring[s % ring] = 0.f; correct_ring[s % ring] = 0; }
+    if (bump_step == 2) adam_coef_update(step_ptr);
   }
   for (int i = threadIdx.x; i < 784; i += blockDim.x) img[i / 28][i % 28] = x[(size_t)b * 784 + i];
   __syncthreads();

@@ -35,6 +35,14 @@ int b200_comm_set_timeout_ms(b200_comm_t h, double ms);
 /* The fused kernel launched on `channel` (the last kernel of a training step) also copies that step's slot of the
  * loss / correct-count rings into pinned host memory: the per-step result the reference prints
  * (horovod/tensorflow_mnist.py:148-149) reaches the host without a copy operation between two steps. */
+/* Push inbox for the latency-bound one-shot buckets: launches of b200_fused_allreduce_adam on `channel` (blocks of at most
+ * 256 threads, one-shot ranges) store each rank's gradient slice into every peer's inbox BEFORE raising the barrier flag,
+ * so the peers' data arrives with the flag (one one-way NVLink latency) instead of being fetched after it (two round
+ * trips).  seg: symmetric segment of 2 * bytes_per_parity bytes. */
+int b200_comm_set_inbox(b200_comm_t h, int channel, int seg, size_t bytes_per_parity);
+/* Fused kernels read the step's Adam coefficients from (ctrl_seg, off) (written once per step by the first kernel of the
+ * step, bump_step = 2 of b200_conv1_pool_fwd / b200_conv1_valid_fwd) instead of computing two fp64 pow() each. */
+int b200_comm_set_coef_cache(b200_comm_t h, int ctrl_seg, size_t off);
 int b200_comm_set_step_mirror(b200_comm_t h, int channel, int ctrl_seg, size_t loss_off, size_t correct_off, int ring,
                               float* host_loss, int* host_correct);
 int b200_comm_set_debug_skew_ns(b200_comm_t h, unsigned max_ns);   /* race hunting: random delay before each barrier arrival */
@@ -105,7 +113,9 @@ int b200_adasum_pair_static(const float* a, const float* b, float* out, int nblo
 /* ---- model kernels, CUDA-core family (first conv, head, fallbacks) ---- */
 /* conv 5x5 SAME Cin=1 + bias + ReLU + maxpool2 (horovod/tensorflow_mnist.py:49-53). step_ptr (may be NULL)
  * is incremented by one when bump_step != 0: the step counter Adam and dropout read; with ring > 0 the
- * new step's slot of the loss/correct rings is cleared at the same time. */
+ * new step's slot of the loss/correct rings is cleared at the same time.  bump_step == 2: step_ptr is the start of the
+ * engine's control block (hyper-parameters at +16 B, beta powers at +96 B) and the step's Adam coefficients are written
+ * to +128 B (see b200_comm_set_coef_cache). */
 int b200_conv1_pool_fwd(const float* x, const void* w_bf16, const void* bias_bf16, void* out_bf16, uint8_t* argmax,
                         int B, int C1, int* step_ptr, int bump_step, float* loss_ring, int* correct_ring, int ring,
                         void* stream);

@@ -270,3 +270,90 @@ def test_adasum_levels_match_tree(n):
             assert torch.allclose(got.cpu(), want, rtol=1e-4, atol=1e-5)
     finally:
         a.close()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("nblocks", [1, 7, 32])
+def test_oneshot_bulk_prefetch_path(n, nblocks):
+    """All ranges one-shot + blocks of <= 256 threads: the peers' slices come in by TMA bulk copies (shared-memory
+    staging, block-contiguous partition).  Ranges of awkward sizes, several steps (both gradient-buffer parities)."""
+    torch.manual_seed(n * 100 + nblocks)
+    sizes = [832, 51264, 11276]
+    N = sum(sizes)
+    rig = Rig(n, N)
+    try:
+        master0 = torch.randn(N, device="cuda")
+        for r in range(n):
+            rig.t(rig.state, 0, torch.float32, r).copy_(master0)
+        pr, mr, vr = master0.clone(), torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        ranges, off = [], 0
+        for sz in sizes:
+            ranges.append((off, sz, 0, 1))
+            off += sz
+        for step in range(1, 5):
+            par = step & 1
+            rig.set_step(step)
+            grads = [torch.randn(N, device="cuda") for _ in range(n)]
+            for r in range(n):
+                rig.t(rig.grad, par * N, torch.float32, r).copy_(grads[r])
+                rig.t(rig.grad, (1 - par) * N, torch.float32, r).fill_(7.0)
+            rig.fused(par, ranges, nblocks=nblocks)
+            torch.cuda.synchronize()
+            g = grads[0].clone()
+            for r in range(1, n):
+                g += grads[r]
+            g *= 1.0 / n
+            adam_step_(pr, g, mr, vr, step, lr=1e-3)
+            w0 = rig.t(rig.w16, 0, bf16, 0, es=2)
+            for r in range(n):
+                assert torch.equal(rig.t(rig.w16, 0, bf16, r, es=2), w0), f"step {step}: rank {r} weights differ from rank 0"
+                assert torch.count_nonzero(rig.t(rig.grad, (1 - par) * N, torch.float32, r)).item() == 0
+                assert torch.allclose(rig.t(rig.state, 0, torch.float32, r), pr, rtol=1e-5, atol=1e-6)
+    finally:
+        rig.close()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("nblocks", [1, 32])
+def test_oneshot_push_inbox_path(n, nblocks):
+    """Push form of the small one-shot buckets: every rank stores its slice into the peers' inboxes in front of its
+    barrier flag; the sum (own gradient + inbox rows, rank order) must equal the pulled one bit for bit on every rank."""
+    import ctypes
+    torch.manual_seed(n * 7 + nblocks)
+    sizes = [832, 51264, 11276]
+    N = sum(sizes)
+    rig = Rig(n, N)
+    try:
+        bpp = (n * N * 4 + 255) // 256 * 256
+        inbox = rig.a.alloc(2 * bpp)
+        for r in range(n):
+            rig.a.view(inbox, 0, 2 * bpp // 4, torch.float32, r).fill_(float("nan"))     # never read before written
+        K.check(K.lib().b200_comm_set_inbox(rig.a.h, 1, inbox, bpp), "set_inbox")
+        master0 = torch.randn(N, device="cuda")
+        for r in range(n):
+            rig.t(rig.state, 0, torch.float32, r).copy_(master0)
+        pr, mr, vr = master0.clone(), torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        ranges, off = [], 0
+        for sz in sizes:
+            ranges.append((off, sz, 0, 1))
+            off += sz
+        for step in range(1, 6):
+            par = step & 1
+            rig.set_step(step)
+            grads = [torch.randn(N, device="cuda") for _ in range(n)]
+            for r in range(n):
+                rig.t(rig.grad, par * N, torch.float32, r).copy_(grads[r])
+            rig.fused(par, ranges, nblocks=nblocks)
+            torch.cuda.synchronize()
+            g = grads[0].clone()
+            for r in range(1, n):
+                g += grads[r]
+            g *= 1.0 / n
+            adam_step_(pr, g, mr, vr, step, lr=1e-3)
+            w0 = rig.t(rig.w16, 0, bf16, 0, es=2)
+            for r in range(n):
+                assert torch.equal(rig.t(rig.w16, 0, bf16, r, es=2), w0), f"step {step}: rank {r} weights differ from rank 0"
+                assert torch.allclose(rig.t(rig.state, 0, torch.float32, r), pr, rtol=1e-5, atol=1e-6)
+    finally:
+        K.lib().b200_comm_set_inbox(rig.a.h, -1, 0, 0)
+        rig.close()

@@ -197,7 +197,7 @@ def test_poison_mode_changes_nothing_when_the_protocol_holds(data, monkeypatch):
         assert np.isfinite(lb) and abs(la - lb) < 2e-3 * max(1.0, abs(la)), (s, la, lb)
     torch.cuda.synchronize()
     assert bool(torch.isfinite(b.master).all())
-    assert (a.w16.float() - b.w16.float()).abs().max().item() < 4e-3
+    assert (a.w16.float() - b.w16.float()).abs().max().item() < 1e-2
 
 
 def test_state_async_snapshot_equals_state_and_is_not_disturbed_by_later_steps(data):
