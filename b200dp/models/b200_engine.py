@@ -638,6 +638,15 @@ class B200Engine(Engine):
             torch.cuda.nvtx.range_push("b200dp.forward")
         if self.poison:
             self.grads[par].zero_()          # the fused kernels left NaN here instead of zeros
+        K.lib().b200_set_stable_weights(1)   # inside a step no kernel reads weights its stream predecessor wrote
+        try:
+            self._train_body(B, par)
+        finally:
+            K.lib().b200_set_stable_weights(0)
+        self.launches_per_step = K.LAUNCHES[0] - c0
+
+    def _train_body(self, B: int, par: int) -> None:
+        nvtx = self._nvtx
         self._forward(B, True)
         self._head(B, True)
         if nvtx:
@@ -649,7 +658,6 @@ class B200Engine(Engine):
             self._backward_and_update(B, par)
         if nvtx:
             torch.cuda.nvtx.range_pop()
-        self.launches_per_step = K.LAUNCHES[0] - c0
 
     # ------------------------------------------------------------------------------------ public
     def _stage_inputs(self, x, y, B: int, *, overlap: bool = False) -> None:

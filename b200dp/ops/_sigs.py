@@ -80,6 +80,7 @@ _SIGS = {
     "b200_l2_flush": (I, [P, SZ, P]),
     "b200_stream_l2_persist": (I, [P, SZ, F, P]),
     "b200_set_pdl": (I, [I]),
+    "b200_set_stable_weights": (I, [I]),
 }
 
 

@@ -21,6 +21,8 @@
 #include "../include/b200dp.h"
 #include "tc_sm100.cuh"
 
+int b200_stable_weights();     // runtime.cu
+
 namespace {
 
 using namespace tc;
@@ -43,6 +45,7 @@ struct HaloParams {
   uint8_t* argmax;
   uint32_t tmem_cols;
   int dbg;             // experiment switches: 1 skip MMAs, 2 skip image loads, 4 skip weight loads
+  int early_w;         // the filter bank was NOT written by the kernel launched just before: load it ahead of the dependency wait
 };
 
 __device__ __forceinline__ void halo_epilogue(const HaloParams& p, const float* sbias, uint32_t taddr, int img, int h0, int lane, int q) {
@@ -117,6 +120,18 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  auto load_filters = [&]() {
+    // filter bank: once per CTA, one barrier per tap so the first MMAs start after 4 KB
+    for (int t = 0; t < ntaps; ++t) {
+      if (p.dbg & 4) { mbar_arrive(wfull + t); continue; }
+      mbar_arrive_expect_tx(wfull + t, (uint32_t)p.wtile_bytes);
+      tma_load_2d(sW + t * p.wtile_bytes, &tmW, wfull + t, 0, t * p.Ci);     // [Ci rows][Co cols]
+    }
+  };
+  // Inside a training step the weights were written by the PREVIOUS step's update, complete long before this kernel's
+  // predecessor even started (every kernel of the chain passes its own dependency wait before it releases its
+  // successor), so the 100 KB filter bank streams in underneath the predecessor's tail instead of after it.
+  if (p.early_w && warp == 0 && elect_one()) load_filters();
   pdl_wait();          // everything above overlapped the previous kernel; its outputs are visible from here on
   pdl_launch_dependents();
   // (the bias, a weight written by the optimizer kernel, is staged by the epilogue warps alone — see below — so the TMA,
@@ -124,14 +139,7 @@ __global__ void __launch_bounds__(320, 1) conv_halo_kernel(const __grid_constant
 
   if (warp == 0) {
     const bool leader = elect_one();
-    if (leader) {
-      // filter bank: once per CTA, one barrier per tap so the first MMAs start after 4 KB
-      for (int t = 0; t < ntaps; ++t) {
-        if (p.dbg & 4) { mbar_arrive(wfull + t); continue; }
-        mbar_arrive_expect_tx(wfull + t, (uint32_t)p.wtile_bytes);
-        tma_load_2d(sW + t * p.wtile_bytes, &tmW, wfull + t, 0, t * p.Ci);     // [Ci rows][Co cols]
-      }
-    }
+    if (leader && !p.early_w) load_filters();
     __syncwarp();
   } else if (warp == 1) {
     // Uniform loops, fully unrolled over taps and K steps; one elected lane issues.  An A descriptor is a constant
@@ -258,6 +266,7 @@ int b200_conv_halo_launch(int mode, const void* act, const void* w, const void* 
   if (cols > 512) return B200_ERR_UNSUPPORTED;
   p.tmem_cols = cols;
   { const char* e = getenv("B200DP_HALO_DBG"); p.dbg = e ? atoi(e) : 0; }
+  p.early_w = b200_stable_weights();
   const size_t smem = 1024 + (size_t)wbytes + 128 + 2 * ((size_t)p.img_bytes + 128) + (ntaps + 12) * 8 + 64 + (size_t)N * 4;
   if (smem > 220 * 1024) return B200_ERR_UNSUPPORTED;
 

@@ -457,7 +457,13 @@ int b200_conv_tc_wgrad_pad(const void* in, const void* dout, float* dw, float* d
   while ((int)cols < p.BN) cols <<= 1;
   p.tmem_cols = cols;
   const int mtiles = (p.npairs + p.G - 1) / p.G, ntile_n = Co / p.BN;
-  int split = (148 * 2) / (mtiles * ntile_n);
+  static int target_ctas = 0;
+  if (!target_ctas) {
+    const char* e = getenv("B200DP_WGRAD_CTAS");      // tuning knob: CTAs the split over pixel tiles aims for
+    target_ctas = e ? atoi(e) : 148;               // one wave: 12.8 us vs 16.3 us at two CTAs per SM (two uneven waves) on the MNIST conv2
+    if (target_ctas < 1) target_ctas = 148;
+  }
+  int split = target_ctas / (mtiles * ntile_n);
   if (split < 1) split = 1;
   if (split > p.ntiles) split = p.ntiles;
   p.tiles_per_split = (p.ntiles + split - 1) / split;

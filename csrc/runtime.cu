@@ -66,6 +66,14 @@ int b200_pdl_enabled() {
 }
 extern "C" int b200_set_pdl(int on) { g_pdl = on ? 1 : 0; return 0; }
 
+// "The weights a kernel reads were not written by the kernel launched just before it" — true for every launch inside a
+// training step (weights change only in the previous step's update).  Kernels launched while it is set may load their
+// weights ahead of the programmatic dependency wait.  Off by default: a caller that writes weights and then launches
+// a convolution right behind that write must not set it.
+static int g_stable_w = 0;
+int b200_stable_weights() { return g_stable_w; }
+extern "C" int b200_set_stable_weights(int on) { g_stable_w = on ? 1 : 0; return 0; }
+
 // Pin [base, base+bytes) in L2 for every kernel launched into `stream` afterwards (also the kernel nodes a capture of that
 // stream creates): hits inside the window are kept with the persisting property, misses stream through.  Experiment
 // switch B200DP_L2_PERSIST of the engine: the Adam state (fp32 master/m/v, 39 MB for the MNIST CNN) is swept once per

@@ -231,6 +231,9 @@ int b200_l2_flush(void* scratch, size_t bytes, void* stream);
 int b200_stream_l2_persist(void* base, size_t bytes, float hit_ratio, void* stream);
 /* Programmatic dependent launch for the step kernels (default on; also B200DP_PDL=0). */
 int b200_set_pdl(int on);
+/* Launches made while this is set promise that the weights they read were not written by the kernel launched just before
+ * them (true inside a training step): such kernels fetch their weights ahead of the programmatic dependency wait. */
+int b200_set_stable_weights(int on);
 
 #ifdef __cplusplus
 }
