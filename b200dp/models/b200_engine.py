@@ -245,6 +245,8 @@ class B200Engine(Engine):
         self._pinned = [(torch.empty(B, 784).pin_memory(), torch.empty(B, dtype=torch.int32).pin_memory(), torch.cuda.Event())
                         for _ in range(3)]
         self._pin_i = 0
+        # (a middle priority for the dense-update branch was measured and lost: 112.4 -> 119.7 us at N=1, 122.8 -> 128.9 at
+        # N=2 — the HBM-bound Adam sweep then runs in front of the conv2 weight gradient and slows the main chain beside it)
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.side_stream = torch.cuda.Stream(device=dev)
         # The step's kernels each want most of the machine, so whichever launches first holds the SMs.  The main chain

@@ -623,8 +623,10 @@ __global__ void __launch_bounds__(128, 8) allgather_acts_kernel(const GatherArgs
 // peer -> shared memory -> local memory through a ring of four slots with mbarrier completion.  Why not plain loads: a
 // peer load stays ~3 us in the SM's load queue, and the loads of whatever convolution CTA shares that SM queue up
 // behind it (measured: the conv2 dgrad beside the load-based gather went from 14 to 29 us).  Bulk copies bypass that
-// queue, and the 64 KB ring makes the blocks settle on the SMs the 128-CTA convolution grids leave free.
-constexpr int GSLOT = 16384, GSLOTS = 4;
+// queue.  The ring is two slots (32 KB) on purpose: with 64 KB the blocks could not share an SM with a resident
+// convolution CTA (186 KB), took whole SMs away from the 128-CTA dgrad that starts right behind them, and pushed 20 of its
+// CTAs into a second wave (measured at N=8: dgrad 13 -> 26 us).  One block per SM x 32 KB = 4.7 MB in flight.
+constexpr int GSLOT = 16384, GSLOTS = 2;     // 32 KB per block: small enough to sit on an SM BESIDE a 186 KB convolution CTA
 
 template <bool EMU>
 __global__ void __launch_bounds__(32) allgather_acts_bulk_kernel(const GatherArgs areal, const GatherArgs* aemu) {
@@ -1220,7 +1222,7 @@ int b200_allgather_acts(b200_comm_t h, int channel, int nblocks, int act_seg, si
   }
   if (!bulk)
     return launch_ranked(c, args, allgather_acts_kernel<false>, allgather_acts_kernel<true>, nblocks, 128, (cudaStream_t)stream);
-  return launch_ranked_smem(c, args, allgather_acts_bulk_kernel<false>, allgather_acts_bulk_kernel<true>, nblocks < 40 ? nblocks : 40, 32,
+  return launch_ranked_smem(c, args, allgather_acts_bulk_kernel<false>, allgather_acts_bulk_kernel<true>, nblocks < 148 ? nblocks : 148, 32,
                             (size_t)GSLOTS * GSLOT + 64, (cudaStream_t)stream);
 }
 
