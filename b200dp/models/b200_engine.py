@@ -573,9 +573,14 @@ class B200Engine(Engine):
         ev_dy = torch.cuda.Event()
         ev_dy.record(main)
         k2 = self.pv("conv2.kernel", w)
+        # Alone (n == 1) the conv2 weight gradient runs behind conv1's on the main chain: beside the dgrad it only stretched
+        # both (112.4 -> 110.5 us/step).  Across ranks it keeps its own branch, so the dense update that waits for SMs is
+        # not pushed further back (serial at N=2: 120.0 -> 131.5 us).
+        serial = _env_flag("B200DP_SERIAL_WGRAD", "1" if self.n == 1 else "0")
         s2.wait_event(ev_dy)
-        with torch.cuda.stream(s2):
-            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
+        if not serial:
+            with torch.cuda.stream(s2):
+                K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
         K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B], pad=self.PAD2)
         ev_dg2 = torch.cuda.Event()
         ev_dg2.record(main)
@@ -590,6 +595,8 @@ class B200Engine(Engine):
             K.conv1_valid_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
         else:
             K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
+        if serial:
+            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
         main.wait_event(ev_s2)
         main.wait_event(ev_s1)
         # every peer reaches this kernel's barrier after its own weight pushes: passing it means the new dense weights of
