@@ -582,6 +582,10 @@ class B200Engine(Engine):
             with torch.cuda.stream(s2):
                 K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
         K.conv_tc_dgrad(self.dy2[:B], k2, self.da1[:B], pad=self.PAD2)
+        if serial:
+            # alone: dgrad -> conv2 wgrad -> conv1 wgrad on one chain; the small-tensor update (which needs the conv2
+            # gradient and rewrites the conv2 weights) then runs underneath conv1's weight gradient
+            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
         ev_dg2 = torch.cuda.Event()
         ev_dg2.record(main)
         with torch.cuda.stream(s2):
@@ -595,8 +599,6 @@ class B200Engine(Engine):
             K.conv1_valid_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
         else:
             K.conv1_wgrad(self.x[:B], self.da1[:B], self.a1[:B], self.am1[:B], self.pv("conv1.kernel", g), self.pv("conv1.bias", g))
-        if serial:
-            K.conv_tc_wgrad(self.a1[:B], self.dy2[:B], self.pv("conv2.kernel", g), None, pad=self.PAD2)
         main.wait_event(ev_s2)
         main.wait_event(ev_s1)
         # every peer reaches this kernel's barrier after its own weight pushes: passing it means the new dense weights of
@@ -911,8 +913,15 @@ class B200Engine(Engine):
             self._gather_sharded()
         else:
             torch.cuda.synchronize()
-        for t in (self.master, self.m, self.v):
-            C.broadcast_(t, root_rank)
+        if (self.T * 3) % 4 == 0 and not self.arena.emulated:
+            # master | m | v are one contiguous range of a segment every peer has mapped: the ranks pull it straight out of
+            # the root's copy (scatter + all-gather of slices above 1 MB) in ONE kernel, with no staging buffer in between
+            from ..parallel.arena import CH_BCAST
+            K.check(K.lib().b200_broadcast(self.arena.h, CH_BCAST, 64, 512, root_rank, self.seg_state, 0, self.seg_state, 0,
+                                           self.T * 3, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "broadcast_state")
+        else:
+            for t in (self.master, self.m, self.v):
+                C.broadcast_(t, root_rank)
         K.cast_f32_to_bf16(self.master, self.w16)
         step, seed = C.broadcast_object((self.global_step, self.seed), root_rank)
         if seed != self.seed or (step & 1) != (self.global_step & 1):

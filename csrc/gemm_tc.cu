@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(192, 2) gemm_tc_kernel(const __grid_constant__
                        : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");     // stores performed before the grid completes
-        if (nr > 1) __threadfence_system();
+        if (nr > 1 && p.tma_push == 2) __threadfence_system();
       }
     } else if (nr > 1) {
       __threadfence_system();   // weights pushed into the peers are visible before this grid completes
@@ -451,7 +451,12 @@ static int gemm_tc_launch(const void* A, const void* B, void* C, float* const* p
     for (int r = 0; r < B200_MAX_RANKS; ++r) p.w16[r] = adam->w16[r];
     p.nranks = adam->nranks; p.param_base = adam->param_base; p.step_ptr = adam->step_ptr; p.hyper = adam->hyper;
     p.gscale = adam->gscale;
-    p.tma_push = wmaps ? 1 : 0;
+    {
+      // wait_group 0 above has already waited for the stores to be performed; the extra system fence (B200DP_PUSH_FENCE=1)
+      // measured as a third of this kernel's stall samples (MEMBAR.SC.SYS + ERRBAR) and is off by default
+      const char* e = getenv("B200DP_PUSH_FENCE");
+      p.tma_push = wmaps ? ((e && e[0] == '1') ? 2 : 1) : 0;
+    }
     p.coef = adam->coef;
   }
   p.C = C; p.M = M; p.N = N; p.K = K; p.ldc = ldc;
