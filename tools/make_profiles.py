@@ -46,7 +46,7 @@ if os.path.exists(so):
         m = re.search(r"Function : (\S+)", line)
         if m:
             cur = short(m.group(1)); counts.setdefault(cur, {}); continue
-        m = re.search(r"\s(UTCHMMA|UTCQMMA|UTMALDG\.\dD|LDTM\S*|STTM\S*|UTCBAR|UTCATOMSWS\S*|UBLKRED\S*|UBLKCP\S*|LDGMC\S*|STGMC\S*|REDGMC\S*|SYNCS\.\S+|RED\.E\.ADD\.F32\S*|HMMA\S*|LDG\.E\.128\S*|ST\.E\.STRONG\.SYS|LD\.E\.STRONG\.SYS|STG\.E\.STRONG\.SYS|LDG\.E\.STRONG\.SYS)", line)
+        m = re.search(r"\s(UTCHMMA|UTCQMMA|UTMALDG\.\dD|UTMASTG\.\dD|LDTM\S*|STTM\S*|UTCBAR|UTCATOMSWS\S*|UBLKRED\S*|UBLKCP\S*|LDGMC\S*|STGMC\S*|REDGMC\S*|SYNCS\.\S+|RED\.E\.ADD\.F32\S*|HMMA\S*|LDG\.E\.128\S*|ST\.E\.STRONG\.SYS|LD\.E\.STRONG\.SYS|STG\.E\.STRONG\.SYS|LDG\.E\.STRONG\.SYS)", line)
         if m and cur:
             k = m.group(1).split(".")[0] + ("." + ".".join(m.group(1).split(".")[1:3]) if "." in m.group(1) else "")
             counts[cur][k] = counts[cur].get(k, 0) + 1
