@@ -244,10 +244,14 @@ def main():
                                  if args.arch == "mnist_cnn" else
                                  f"keras128(conv3x3x{eng.C1}-conv3x3x{eng.C2}-pool-dropout0.25-dense{eng.D}-dropout0.5-dense10, ")
                                 + f"{spec.num_params} params)", "global_batch": B * world_size, "per_gpu_batch": B, "seq_len": None,
-                       "parallelism": f"dp{world_size}", "optimizer": "Adam(lr=0.001*size) fused into the NVLink allreduce",
+                       "parallelism": f"dp{world_size}",
+                       "optimizer": ("Adam(lr=0.001*size) in the dense wgrad GEMM's epilogue and in the closing collective" if eng.dense_fused
+                                     else "Adam(lr=0.001*size) fused into the NVLink allreduce"),
                        "allreduce": ({"dense.kernel": "none: all-gather of dz + activation slices (bf16) -> wgrad GEMM over the global batch "
                                                       "-> Adam in the GEMM epilogue -> bf16 weights stored to all ranks",
-                                      "rest": "oneshot (conv2/out/bias underneath backward; conv1 exposed)", "wire": "bf16 activations / fp32 small grads"}
+                                      "rest": ("one push-form one-shot kernel at the end of the step (inbox stores in front of the barrier flag)"
+                                               if not eng.comm_rest else "oneshot (conv2/out/bias underneath the conv1 wgrad; conv1 at the end)"),
+                                      "wire": "bf16 activations / fp32 small grads"}
                                      if eng.dense_fused else
                                      {"dense.kernel": ["oneshot", "twoshot", "nvls", "gemm+reduce-scatter fused, then two-shot tail"][eng.comm_dense[0][2]],
                                       "rest": ["oneshot", "twoshot", "nvls"][eng.comm_rest[1][2]], "wire": "fp32"}),
