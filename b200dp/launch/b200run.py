@@ -182,7 +182,14 @@ class _Pump(threading.Thread):
 def launch_once(args, slots: List[Slot], restart_count: int) -> int:
     np_ = len(slots)
     master_addr = args.master_addr or ("127.0.0.1" if all(_is_local(s.host) for s in slots) else slots[0].host)
-    master_port = args.master_port or _free_port()
+    if args.master_port:
+        master_port = args.master_port
+    elif _is_local(slots[0].host):
+        master_port = _free_port()          # rank 0 binds it on this host: probing here is meaningful
+    else:
+        # rank 0 lives on another host, where a port probed here says nothing: a fixed, documented default (override
+        # with --master-port), spread by the restart count so a relaunch does not meet the old socket in TIME_WAIT
+        master_port = 29512 + (restart_count % 16)
     base_env = dict(os.environ)
     exports: Dict[str, str] = {}
     for e in args.exports:

@@ -92,3 +92,27 @@ def test_alias_package_matches():
     assert k.init is hvd.init
     from k8s_distributed_deeplearning_b200.models import spec
     assert spec.get_spec().num_params == 3274634
+
+
+def test_gpu_data_plane_refuses_ranks_on_different_hosts(monkeypatch):
+    """The CUDA data plane is one NVSwitch domain (peer memory mapped with CUDA IPC).  Ranks on different hosts must get a
+    sentence from init(), not an opaque cudaIpcOpenMemHandle failure."""
+    import torch.distributed as dist
+    from b200dp.runtime import world as W
+
+    def fake_gather(out, obj):
+        out[0], out[1] = "pod-a", "pod-b"
+
+    monkeypatch.setattr(dist, "all_gather_object", fake_gather)
+    w = W.World(rank=0, size=2, local_rank=0, local_size=1, host="pod-a")
+    with pytest.raises(RuntimeError, match="single-node"):
+        W._require_single_node(w)
+
+    def same_host(out, obj):
+        for i in range(len(out)):
+            out[i] = "pod-a"
+
+    monkeypatch.setattr(dist, "all_gather_object", same_host)
+    W._require_single_node(w)
+    with pytest.raises(RuntimeError, match="exceeds"):
+        W._require_single_node(W.World(rank=0, size=9, local_rank=0, local_size=9, host="pod-a"))

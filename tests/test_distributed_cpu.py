@@ -173,3 +173,20 @@ def test_elastic_resize_relaunches_with_the_new_world_size(tmp_path):
         assert d["restart"] == 1 and d["first_batch"] == 4 and d["final_batch"] == 12 and d["global_step"] == 12
         assert d["resets"] == [1] and d["commits"] == 3
     assert len({d["digest"] for d in res}) == 1
+
+
+def test_keras_example_resumes_from_its_epoch_checkpoint_after_a_restart(tmp_path):
+    """`b200run --max-restarts` relaunches the Keras script after a rank died; the relaunch must continue from the newest
+    epoch checkpoint instead of quietly starting at epoch 0 (the reference script has no resume path of its own)."""
+    args = ["--num-steps", "32", "--batch-size", "32", "--test-samples", "64", "--log-dir", str(tmp_path / "logs"),
+            "--checkpoint-dir", str(tmp_path / "ck"), "--export-dir", str(tmp_path / "final_model")]
+    # 512 // (32*2) = 8 steps per epoch, 4 epochs; rank 1 dies at step 20 (inside epoch 3), epochs 1-2 were checkpointed
+    # whenever val_loss improved (the first epoch always is)
+    r = _example("tensorflow_mnist_gpu.py", tmp_path, 2, args, env={"B200DP_FAULT": "1:20"},
+                 extra=["--max-restarts", "1", "--grace-secs", "2"])
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "restart 1/1" in r.stderr and "resuming from mnist-" in r.stderr
+    recs = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    ep = [d["epoch"] for d in recs if d["event"] == "epoch_end"]
+    assert ep[-1] == 4 and ep.count(1) == 1, ep    # epoch 1 ran once: the relaunch did not start over
+    assert os.path.exists(tmp_path / "final_model" / "model.safetensors")

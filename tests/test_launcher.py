@@ -129,3 +129,35 @@ def test_mpirun_wdir_and_output_filename(tmp_path):
     assert r.returncode == 0, r.stderr
     assert r.stdout.count(f"cwd {wd}") == 2
     assert sorted(os.listdir(logs)) == ["rank-0.log", "rank-1.log"] and f"cwd {wd} 1" in (logs / "rank-1.log").read_text()
+
+
+def test_master_port_for_a_remote_rank0_is_not_probed_locally(monkeypatch):
+    """The rendezvous port is bound by rank 0 on ITS host.  With rank 0 on this host a free port is probed; with rank 0 on
+    another host a local probe would be meaningless, so a fixed default (or --master-port) is used."""
+    seen = {}
+
+    class FakeProc:
+        pid = 1
+        stdout = stderr = None
+
+        def poll(self):
+            return 0
+
+        def wait(self, timeout=None):
+            return 0
+
+    def fake_popen(cmd, **kw):
+        seen.setdefault("envs", []).append(kw.get("env") or {})
+        seen.setdefault("cmds", []).append(cmd)
+        import io
+        p = FakeProc()
+        p.stdout, p.stderr = io.BytesIO(b""), io.BytesIO(b"")
+        return p
+
+    monkeypatch.setattr(L.subprocess, "Popen", fake_popen)
+    args = L.build_parser().parse_args(["-np", "2", "-H", "otherhost:2", "python", "x.py"])
+    args.command = ["python", "x.py"]
+    slots = L.map_by_slot(L.parse_hosts_arg("otherhost:2"), 2)
+    assert L.launch_once(args, slots, 0) == 0
+    joined = " ".join(" ".join(c) if isinstance(c, (list, tuple)) else str(c) for c in seen["cmds"])
+    assert "MASTER_PORT=29512" in joined and "MASTER_ADDR=otherhost" in joined, joined[:400]

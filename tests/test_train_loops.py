@@ -38,6 +38,11 @@ def test_session_stops_at_step_logs_and_checkpoints(tmp_path, data, capsys):
     out = capsys.readouterr()
     steps = [json.loads(l)["step"] for l in out.out.splitlines() if '"train_step"' in l]
     assert steps == [1, 11, 21]                                         # every 10 iterations
+    recs = [json.loads(l) for l in out.out.splitlines() if '"train_step"' in l]
+    # the record carries what the reference's log line carries, in fields: the interval as time per step, plus rate and lr
+    assert recs[0]["lr"] == pytest.approx(2e-3) and recs[0]["batch"] == 32 and "step_ms" not in recs[0]
+    for r in recs[1:]:
+        assert r["step_ms"] > 0 and r["images_per_sec"] == pytest.approx(32 * hvd.size() / (r["step_ms"] / 1e3), rel=0.05)
     files = sorted(os.listdir(tmp_path / "ck"))
     assert "latest" in files and "ckpt-25.safetensors" in files and "ckpt-10.safetensors" in files
     with pytest.raises(RuntimeError):
