@@ -182,3 +182,113 @@ def test_twoshot_mutants_are_caught(variant):
         except Violation:
             caught += 1
     assert caught > 0, f"mutant {variant} survived every schedule"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The fused dense step (round 2; b200dp/models/b200_engine.py::_backward_fused): two barriers per step.
+#
+#   step t on rank r:
+#     forward  : write act[r] = (r, t)  (a2 and dz: what the peers will gather); READ every slice of w16[r]  -> version t
+#     dgrad    : READ every slice of w16[r] again                                                             -> version t
+#     barrier G(t)   — launched only after this rank's dgrad
+#     gather   : READ act[q] of every rank q                      -> must be exactly (q, t)
+#     GEMM+Adam: owner r stores w16[q][r] = t+1 into EVERY rank q (TMA stores into peer memory)
+#     closing collective, push form: store my small gradient into inbox[q][t & 1][r] of every peer q, THEN raise flag E(t);
+#                wait for every peer's E(t); READ inbox[r][t & 1][q] -> must be exactly (q, t)
+#   then step t+1 overwrites act[r] and reads version t+1 of the weights.
+# Hazards and what prevents them: a push landing while the target still reads version t (G: arrival after the dgrad);
+# act[r] overwritten while a peer still gathers it, or step t+1 starting before every owner's push landed (E: arrival after
+# the own gather and the own pushes); an inbox row overwritten before it was consumed (two parities + E of the step between).
+# ---------------------------------------------------------------------------------------------------------------------
+def fused_proc(r, n, steps, mem, variant):
+    def arrive(name, t):
+        for q in range(n):
+            mem[name][q][r] = t + 1
+            yield
+
+    def wait(name, t):
+        while any(mem[name][r][q] < t + 1 for q in range(n)):
+            yield
+
+    nin = 1 if variant == "single_inbox" else 2
+    for t in range(steps):
+        mem["act"][r] = ("partial", r, t)                    # conv2 forward / head write a2, dz
+        yield
+        mem["act"][r] = (r, t)
+        yield
+        for phase in range(2):                               # dense forward, then dense dgrad: both read the working weights
+            if variant == "gather_before_dgrad" and phase == 1:
+                yield from arrive("G", t)                    # BUG under test: tells the peers "done with the old weights" too early
+            for s in range(n):
+                if mem["w16"][r][s] != t:
+                    raise Violation(f"rank {r} step {t}: slice {s} of its working weights is version {mem['w16'][r][s]}")
+                yield
+        if variant != "gather_before_dgrad":
+            yield from arrive("G", t)
+        yield from wait("G", t)
+        for q in range(n):                                   # gather
+            if mem["act"][q] != (q, t):
+                raise Violation(f"rank {r} step {t}: gathered {mem['act'][q]} from rank {q}")
+            yield
+        for q in range(n):                                   # owner r: weight push
+            mem["w16"][q][r] = t + 1
+            yield
+        for q in range(n):                                   # closing collective: inbox stores first ...
+            if q != r:
+                mem["inbox"][q][t % nin][r] = (r, t)
+                yield
+        if variant != "no_closing_barrier":
+            yield from arrive("E", t)                        # ... then the flag
+            yield from wait("E", t)
+            for q in range(n):
+                if q != r and mem["inbox"][r][t % nin][q] != (q, t):
+                    raise Violation(f"rank {r} step {t}: inbox row of rank {q} holds {mem['inbox'][r][t % nin][q]}")
+                yield
+        mem["reduced"][r] = t + 1
+
+
+def run_fused(n, steps, seed, variant="correct"):
+    rng = random.Random(seed)
+    mem = {"act": [None] * n, "w16": [[0] * n for _ in range(n)], "G": [[0] * n for _ in range(n)], "E": [[0] * n for _ in range(n)],
+           "inbox": [[[None] * n for _ in range(2)] for _ in range(n)], "reduced": [0] * n}
+    procs = {r: fused_proc(r, n, steps, mem, variant) for r in range(n)}
+    slow, ticks = rng.randrange(n), 0
+    while procs:
+        ticks += 1
+        if ticks % 43 == 0:
+            slow = rng.randrange(n)
+        r = rng.choice(list(procs))
+        if r == slow and len(procs) > 1 and rng.random() < 0.85:
+            continue
+        try:
+            next(procs[r])
+        except StopIteration:
+            del procs[r]
+        if ticks > 3_000_000:
+            raise RuntimeError("model deadlocked")
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_fused_dense_step_is_race_free_with_gather_and_closing_barriers(n):
+    for seed in range(150):
+        run_fused(n, steps=8, seed=seed)
+
+
+def test_fused_step_needs_no_second_inbox_but_the_general_entry_point_does():
+    """With TWO barriers per step a single inbox would do: a peer reaches its next inbox store only through G(t+1), which
+    this rank joins after it has consumed inbox(t).  The inbox is double-buffered anyway because b200_comm_set_inbox serves
+    any one-shot launch, and with ONE barrier per step (the plain gradient-buffer protocol at the top of this file) a
+    fast rank's stores of step t+1 would land in rows a slow rank has not summed yet."""
+    for seed in range(150):
+        run_fused(4, steps=6, seed=seed, variant="single_inbox")
+
+
+@pytest.mark.parametrize("variant", ["gather_before_dgrad", "no_closing_barrier"])
+def test_fused_step_mutants_are_caught(variant):
+    caught = 0
+    for seed in range(300):
+        try:
+            run_fused(4, steps=6, seed=seed, variant=variant)
+        except Violation:
+            caught += 1
+    assert caught > 0, f"mutant {variant} survived every schedule"
