@@ -31,7 +31,8 @@ def _check(res, np_, algo):
         assert d["nccl_built"] is True
         for k, v in d.items():
             if k.startswith(("avg_", "sum_", "bcast_")) or k in ("adasum", "losses_finite", "replicas_bitwise_identical", "still_identical",
-                                                                               "identical_after_skewed_stress", "stress_loss_finite"):
+                                                                               "identical_after_skewed_stress", "stress_loss_finite",
+                                                                               "identical_after_compute_delay_stress", "delay_loss_finite"):
                 assert v is True, (d["rank"], k)
         assert d["bf16_avg"] == pytest.approx((np_ - 1) / 2)
         assert d["int_sum"] == np_ * (np_ + 1) // 2

@@ -121,6 +121,16 @@ digests = hvd.allgather_object(hashlib.sha256(eng.w16.cpu().view(torch.int16).nu
 res["identical_after_skewed_stress"] = len(set(digests)) == 1
 res["stress_loss_finite"] = bool(np.isfinite(eng.train_step(xs[0, r], ys[0, r]).loss_value()))
 hvd.world().arena.set_debug_skew_ns(0)
+# compute delay instead of barrier skew: one rank at a time starts its step 100-300 us late (a spin kernel in front of the
+# graph launch), so the others sit in the gather / closing barriers with their buffers of the previous step still live
+for s in range(400):
+    if r == (s // 20) % n:
+        torch.cuda._sleep(int(2e5) * (1 + s % 3))
+    eng.train_step(xs[s % 6, r], ys[s % 6, r])
+torch.cuda.synchronize()
+digests = hvd.allgather_object(hashlib.sha256(eng.w16.cpu().view(torch.int16).numpy().tobytes()).hexdigest())
+res["identical_after_compute_delay_stress"] = len(set(digests)) == 1
+res["delay_loss_finite"] = bool(np.isfinite(eng.train_step(xs[0, r], ys[0, r]).loss_value()))
 # End of run: the other ranks go straight to shutdown while rank 0 dawdles and only then reads the (sharded) state for
 # its final save.  shutdown() is collective, so the peers' memory is still mapped and valid when rank 0 pulls from it.
 if r == 0:
