@@ -371,7 +371,7 @@ class B200Engine(Engine):
         dk = self.spec.param("dense.kernel")
         self.gemm_rs = bool(self.reduce and not adasum and self.tc_dense and self.comm_dense[0][2] == autoselect.TWOSHOT
                             and self.F % self.n == 0 and self.comm_dense[0][0] == dk.offset and self.comm_dense[0][1] == dk.numel
-                            and _env_flag("B200DP_GEMM_RS"))
+                            and _env_flag("B200DP_GEMM_RS") and not _env_flag("B200DP_DETERMINISTIC", "0"))
         if self.gemm_rs:
             self.comm_dense = [(dk.offset, dk.numel, 3, 1)]
         self.comm_rest = [rng(by["dense.bias+out."]), rng(by["conv1."]), rng(by["conv2."])]
